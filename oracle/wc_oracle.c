@@ -1,0 +1,427 @@
+/*
+ * oracle/wc_oracle.c -- TEST INFRASTRUCTURE, NOT PRODUCT CODE (see wc_oracle.h).
+ *
+ * CPU restatement of /root/reference/main.cu's word count.  Parity: PINNED
+ * against the reference's own source run on host cores (oracle/_ref/main_cpu)
+ * -- tests/test_oracle_vs_reference.py and tests/golden/.
+ *
+ * Each function cites the reference lines it restates.  Nothing is copied: the
+ * reference works on fixed-size structs (main.cu:16-33); this file works on
+ * (offset, length) views of the raw input so that none of its capacities
+ * (10 chunks, 20 words per chunk, 19-byte words, 10 rows) exist here.
+ */
+#define _GNU_SOURCE
+#include "wc_oracle.h"
+
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ------------------------------------------------------------------------- */
+/* Splitter: main.cu:174-206                                                 */
+/* ------------------------------------------------------------------------- */
+
+typedef void (*orc_emit_fn)(void *ctx, uint64_t off, uint32_t len, uint64_t flush_off);
+
+typedef struct {
+    size_t pos;   /* where the next fgets starts */
+    size_t clen;  /* bytes fgets consumed (0: nothing left)          main.cu:179 */
+    size_t slen;  /* strlen() of the zero-filled line buffer          main.cu:185,187 */
+} orc_chunk;
+
+/* One `memset(szLine,0,100); fgets(szLine,100,pFile)` step (main.cu:178-179):
+ * at most linecap bytes, ending after the first '\n'.  The buffer is zeroed
+ * first, so a failed read leaves "" and strlen() stops at the first NUL. */
+static int next_chunk(const uint8_t *d, size_t n, int linecap, orc_chunk *c) {
+    c->pos += c->clen;
+    if (c->pos >= n) { c->clen = 0; c->slen = 0; return 0; }
+    size_t room = n - c->pos;
+    if (linecap > 0 && room > (size_t)linecap) room = (size_t)linecap;
+    const uint8_t *nl = memchr(d + c->pos, '\n', room);
+    c->clen = nl ? (size_t)(nl - (d + c->pos)) + 1 : room;
+    const uint8_t *z = memchr(d + c->pos, 0, c->clen);
+    c->slen = z ? (size_t)(z - (d + c->pos)) : c->clen;
+    return 1;
+}
+
+static void split(const uint8_t *d, size_t n, uint64_t base, int linecap, orc_emit_fn emit,
+                  void *ctx, orc_result *st) {
+    orc_chunk c = {0, 0, 0};
+    st->stop = base + n;
+    for (;;) { /* while(!feof(pFile))  main.cu:176 -- an exhausted file yields "" below */
+        if (!next_chunk(d, n, linecap, &c)) break;
+        if (c.clen > st->max_line) st->max_line = c.clen;
+        if (c.slen < c.clen) st->n_nul++;
+        if (c.slen < 2) { st->stop = base + c.pos; break; } /* main.cu:185-186 */
+        st->n_chunks++;
+        size_t wstart = c.pos; /* nIndex = 0 per chunk, main.cu:183 */
+        for (size_t i = 0; i < c.slen; i++) { /* main.cu:187 */
+            uint8_t b = d[c.pos + i];
+            if (b == ' ' || b == 0x0d || b == 0x0A) { /* main.cu:188 */
+                size_t at = c.pos + i;
+                emit(ctx, base + wstart, (uint32_t)(at - wstart), base + at); /* main.cu:190-194 */
+                wstart = at + 1;
+                if (b == 0x0d) { st->n_cr++; break; } /* main.cu:195-196 */
+            }
+        }
+        /* bytes after the last delimiter are dropped: no flush after the loop,
+         * main.cu:198-203 */
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* Literal reducer: main.cu:37-54 (map), 57-67 (compare), 69-108 (reduce)     */
+/* ------------------------------------------------------------------------- */
+
+typedef struct {
+    const uint8_t *data;
+    orc_result *r;
+    size_t cap;
+    int seen_nonempty;
+} lit_ctx;
+
+/* compare(sz1 = row word, sz2 = new word): true iff sz2 is a prefix of sz1;
+ * sz1 is NUL-terminated, so a longer sz2 fails at the terminator. main.cu:57-67 */
+static int lit_is_prefix(const uint8_t *row, uint32_t row_len, const uint8_t *w, uint32_t w_len) {
+    if (w_len > row_len) return 0;
+    return memcmp(row, w, w_len) == 0;
+}
+
+static void lit_emit(void *vctx, uint64_t off, uint32_t len, uint64_t flush_off) {
+    lit_ctx *c = (lit_ctx *)vctx;
+    orc_result *r = c->r;
+    r->n_flush++;
+    if (len == 0) r->n_empty++;
+    /* scan rows j = 0..nIndex inclusive, main.cu:81-89 */
+    for (size_t j = 0; j < r->n_rows; j++) {
+        if (lit_is_prefix(c->data + r->rows[j].off, r->rows[j].len, c->data + off, len)) {
+            r->rows[j].count++; /* main.cu:85 */
+            return;
+        }
+    }
+    /* j == nIndex: the slot past the rows is all zero (cudaMemset, main.cu:154):
+     * only the empty word matches it, and that increment is overwritten when
+     * the slot is later filled (main.cu:103) -> the word is lost. */
+    if (len == 0) { r->n_lost_empty++; return; }
+    if (r->n_rows == c->cap) {
+        c->cap = c->cap ? c->cap * 2 : 64;
+        r->rows = (orc_row *)realloc(r->rows, c->cap * sizeof(orc_row));
+    }
+    orc_row *row = &r->rows[r->n_rows++]; /* append, main.cu:93-104 */
+    row->off = off; row->len = len; row->count = 1; row->first = flush_off;
+}
+
+int orc_literal(const uint8_t *data, size_t n, int linecap, orc_result *out) {
+    memset(out, 0, sizeof(*out));
+    lit_ctx c = {data, out, 0, 0};
+    split(data, n, 0, linecap, lit_emit, &c, out);
+    for (size_t j = 0; j < out->n_rows; j++) out->total += out->rows[j].count; /* main.cu:214 */
+    return 0;
+}
+
+/* ------------------------------------------------------------------------- */
+/* Fast path: exact counts + first occurrence, then SURVEY.md A.3 post-pass    */
+/* ------------------------------------------------------------------------- */
+
+typedef struct {
+    uint64_t off, first, hash;
+    int64_t count;
+    uint32_t len, used;
+} fent;
+
+typedef struct {
+    const uint8_t *data;
+    fent *e;
+    size_t cap, n; /* cap is a power of two */
+    uint64_t n_flush, n_empty, n_lost_empty, p0;
+    int seen_nonempty;
+} fmap;
+
+static inline uint64_t hash_bytes(const uint8_t *p, size_t len) {
+    uint64_t h = 0x9E3779B97F4A7C15ull ^ (len * 0xff51afd7ed558ccdull);
+    while (len >= 8) {
+        uint64_t v; memcpy(&v, p, 8);
+        h = (h ^ v) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
+        p += 8; len -= 8;
+    }
+    if (len) {
+        uint64_t v = 0; memcpy(&v, p, len);
+        h = (h ^ v) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
+    }
+    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+    return h;
+}
+
+static void fmap_init(fmap *m, const uint8_t *data, size_t cap) {
+    memset(m, 0, sizeof(*m));
+    m->data = data; m->cap = cap;
+    m->e = (fent *)calloc(cap, sizeof(fent));
+    m->p0 = UINT64_MAX;
+}
+
+static void fmap_add(fmap *m, uint64_t hash, uint64_t off, uint32_t len, int64_t count, uint64_t first);
+
+static void fmap_grow(fmap *m) {
+    fent *old = m->e; size_t ocap = m->cap;
+    m->cap = ocap * 2; m->n = 0;
+    m->e = (fent *)calloc(m->cap, sizeof(fent));
+    for (size_t i = 0; i < ocap; i++)
+        if (old[i].used) fmap_add(m, old[i].hash, old[i].off, old[i].len, old[i].count, old[i].first);
+    free(old);
+}
+
+static void fmap_add(fmap *m, uint64_t hash, uint64_t off, uint32_t len, int64_t count, uint64_t first) {
+    size_t mask = m->cap - 1, i = (size_t)hash & mask;
+    for (;;) {
+        fent *e = &m->e[i];
+        if (!e->used) {
+            e->used = 1; e->hash = hash; e->off = off; e->len = len; e->count = count; e->first = first;
+            if (++m->n * 10 > m->cap * 7) fmap_grow(m);
+            return;
+        }
+        if (e->hash == hash && e->len == len && memcmp(m->data + e->off, m->data + off, len) == 0) {
+            e->count += count;
+            if (first < e->first) e->first = first;
+            return;
+        }
+        i = (i + 1) & mask;
+    }
+}
+
+static void fast_emit(void *vctx, uint64_t off, uint32_t len, uint64_t flush_off) {
+    fmap *m = (fmap *)vctx;
+    m->n_flush++;
+    if (len == 0) {
+        m->n_empty++;
+        if (!m->seen_nonempty) m->n_lost_empty++;
+        return;
+    }
+    if (!m->seen_nonempty) { m->seen_nonempty = 1; m->p0 = flush_off; }
+    fmap_add(m, hash_bytes(m->data + off, len), off, len, 1, flush_off);
+}
+
+static int cmp_lex(const void *a, const void *b, void *vdata) {
+    const uint8_t *d = (const uint8_t *)vdata;
+    const fent *x = (const fent *)a, *y = (const fent *)b;
+    uint32_t l = x->len < y->len ? x->len : y->len;
+    int c = memcmp(d + x->off, d + y->off, l);
+    if (c) return c;
+    return (x->len > y->len) - (x->len < y->len);
+}
+
+static int cmp_first(const void *a, const void *b) {
+    const orc_row *x = (const orc_row *)a, *y = (const orc_row *)b;
+    return (x->first > y->first) - (x->first < y->first);
+}
+
+/* Turn a table of exact counts into the rows main.cu would print. */
+static void finalize(fmap *m, int mode, orc_result *out) {
+    size_t nd = 0;
+    fent *v = (fent *)malloc((m->n ? m->n : 1) * sizeof(fent));
+    for (size_t i = 0; i < m->cap; i++)
+        if (m->e[i].used) v[nd++] = m->e[i];
+    out->n_flush = m->n_flush; out->n_empty = m->n_empty; out->n_lost_empty = m->n_lost_empty;
+    out->rows = NULL; out->n_rows = 0; out->total = 0;
+    if (nd == 0) { free(v); return; }
+
+    if (mode == ORC_MODE_EXACT) {
+        out->rows = (orc_row *)malloc(nd * sizeof(orc_row));
+        for (size_t i = 0; i < nd; i++) {
+            orc_row r = {v[i].off, v[i].len, v[i].count, v[i].first};
+            out->rows[i] = r; out->total += v[i].count;
+        }
+        out->n_rows = nd;
+        qsort(out->rows, nd, sizeof(orc_row), cmp_first);
+        free(v);
+        return;
+    }
+
+    /* A.3: owner(w) = the earliest-first-seen distinct word that has w as a
+     * prefix.  In bytewise order the words having prefix w are a contiguous
+     * run that starts at w, so one sweep with a stack of open prefixes gives
+     * every run's minimum. */
+    qsort_r(v, nd, sizeof(fent), cmp_lex, (void *)m->data);
+    size_t *owner = (size_t *)malloc(nd * sizeof(size_t));
+    size_t *stk = (size_t *)malloc(nd * sizeof(size_t));
+    size_t *best = (size_t *)malloc(nd * sizeof(size_t)); /* argmin(first) of the open run */
+    size_t sp = 0;
+    for (size_t i = 0; i <= nd; i++) {
+        while (sp > 0) {
+            size_t t = stk[sp - 1];
+            int open = i < nd && v[t].len <= v[i].len &&
+                       memcmp(m->data + v[t].off, m->data + v[i].off, v[t].len) == 0;
+            if (open) break;
+            owner[t] = best[sp - 1];
+            if (sp > 1 && v[best[sp - 1]].first < v[best[sp - 2]].first) best[sp - 2] = best[sp - 1];
+            sp--;
+        }
+        if (i < nd) { stk[sp] = i; best[sp] = i; sp++; }
+    }
+    int64_t *acc = (int64_t *)calloc(nd, sizeof(int64_t));
+    size_t nrows = 0;
+    for (size_t i = 0; i < nd; i++) { acc[owner[i]] += v[i].count; nrows += owner[i] == i; }
+    out->rows = (orc_row *)malloc(nrows * sizeof(orc_row));
+    for (size_t i = 0; i < nd; i++)
+        if (owner[i] == i) {
+            orc_row r = {v[i].off, v[i].len, acc[i], v[i].first};
+            out->rows[out->n_rows++] = r;
+        }
+    qsort(out->rows, out->n_rows, sizeof(orc_row), cmp_first);
+    /* S13: empty words after the first non-empty one increment row 0 */
+    out->rows[0].count += (int64_t)(m->n_empty - m->n_lost_empty);
+    for (size_t i = 0; i < out->n_rows; i++) out->total += out->rows[i].count;
+    free(acc); free(best); free(stk); free(owner); free(v);
+}
+
+int orc_fast(const uint8_t *data, size_t n, int mode, orc_result *out) {
+    memset(out, 0, sizeof(*out));
+    fmap m; fmap_init(&m, data, 1u << 16);
+    split(data, n, 0, ORC_LINECAP_INF, fast_emit, &m, out);
+    finalize(&m, mode, out);
+    free(m.e);
+    return 0;
+}
+
+/* ---- multi-threaded variant: line-aligned slices, per-thread tables ------- */
+
+typedef struct {
+    const uint8_t *data; size_t lo, hi;
+    fmap m; orc_result st;
+} slice_job;
+
+static void *slice_main(void *arg) {
+    slice_job *j = (slice_job *)arg;
+    /* the table is keyed on absolute offsets into data */
+    fmap_init(&j->m, j->data, 1u << 16);
+    memset(&j->st, 0, sizeof(j->st));
+    /* split() reports offsets relative to its own buffer start plus `base`;
+     * passing the slice pointer with base = lo keeps them absolute. */
+    split(j->data + j->lo, j->hi - j->lo, j->lo, ORC_LINECAP_INF, fast_emit, &j->m, &j->st);
+    return NULL;
+}
+
+int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_result *out) {
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads == 1 || n < (1u << 16)) return orc_fast(data, n, mode, out);
+    memset(out, 0, sizeof(*out));
+    slice_job *jobs = (slice_job *)calloc((size_t)nthreads, sizeof(slice_job));
+    pthread_t *th = (pthread_t *)calloc((size_t)nthreads, sizeof(pthread_t));
+    size_t prev = 0;
+    int nj = 0;
+    for (int t = 0; t < nthreads && prev < n; t++) {
+        size_t want = (t + 1 == nthreads) ? n : (size_t)((double)n * (t + 1) / nthreads);
+        if (want < prev) want = prev;
+        size_t hi = n;
+        if (want < n) { /* move the cut to the next line start: no state crosses it */
+            const uint8_t *nl = memchr(data + want, '\n', n - want);
+            hi = nl ? (size_t)(nl - data) + 1 : n;
+        }
+        if (hi == prev) continue;
+        jobs[nj].data = data; jobs[nj].lo = prev; jobs[nj].hi = hi;
+        prev = hi; nj++;
+    }
+    for (int t = 0; t < nj; t++) pthread_create(&th[t], NULL, slice_main, &jobs[t]);
+    for (int t = 0; t < nj; t++) pthread_join(th[t], NULL);
+
+    fmap m; fmap_init(&m, data, 1u << 16);
+    out->stop = n;
+    for (int t = 0; t < nj; t++) {
+        slice_job *j = &jobs[t];
+        if (!m.seen_nonempty) {
+            /* empties before the job-wide first non-empty word are lost (S13) */
+            m.n_lost_empty += j->m.seen_nonempty ? j->m.n_lost_empty : j->m.n_empty;
+            if (j->m.seen_nonempty) { m.seen_nonempty = 1; m.p0 = j->m.p0; }
+        }
+        m.n_flush += j->m.n_flush; m.n_empty += j->m.n_empty;
+        for (size_t i = 0; i < j->m.cap; i++)
+            if (j->m.e[i].used)
+                fmap_add(&m, j->m.e[i].hash, j->m.e[i].off, j->m.e[i].len, j->m.e[i].count, j->m.e[i].first);
+        out->n_chunks += j->st.n_chunks; out->n_cr += j->st.n_cr; out->n_nul += j->st.n_nul;
+        if (j->st.max_line > out->max_line) out->max_line = j->st.max_line;
+        if (j->st.stop < j->hi) { out->stop = j->st.stop; break; } /* main.cu:185: later slices never ran */
+    }
+    finalize(&m, mode, out);
+    free(m.e);
+    for (int t = 0; t < nj; t++) free(jobs[t].m.e);
+    free(jobs); free(th);
+    return 0;
+}
+
+static void mark_emit(void *vctx, uint64_t off, uint32_t len, uint64_t flush_off) {
+    (void)off; (void)len;
+    ((uint8_t *)vctx)[flush_off] = 1;
+}
+
+uint64_t orc_split_flushes(const uint8_t *data, size_t n, int linecap, uint8_t *flush) {
+    orc_result st; memset(&st, 0, sizeof(st));
+    memset(flush, 0, n);
+    split(data, n, 0, linecap, mark_emit, flush, &st);
+    return st.stop;
+}
+
+void orc_free(orc_result *r) {
+    free(r->rows);
+    r->rows = NULL; r->n_rows = 0;
+}
+
+/* ------------------------------------------------------------------------- */
+/* Byte-parallel statement of the splitter                     */
+/* ------------------------------------------------------------------------- */
+
+uint64_t orc_flush_formula(const uint8_t *b, size_t n, uint8_t *flush) {
+    /* STOP: first line start i at which the line's strlen() is < 2:
+     *   b[i]=='\n' (blank line), b[i]==0, b[i+1]==0, or a 1-byte unterminated tail */
+    uint64_t stop = n;
+    int64_t last_lf = -1, last_kill = -1;
+    memset(flush, 0, n);
+    for (size_t i = 0; i < n; i++) {
+        int line_start = (i == 0) || b[i - 1] == '\n';
+        if (line_start) {
+            int short_line = b[i] == '\n' || b[i] == 0 || (i + 1 < n && b[i + 1] == 0) || (i + 1 == n);
+            if (short_line) { stop = i; break; }
+        }
+        int delim = b[i] == ' ' || b[i] == 0x0d || b[i] == 0x0A;
+        int live = last_kill <= last_lf; /* no CR / NUL earlier on this line */
+        if (delim && live) flush[i] = 1;
+        if (b[i] == 0x0d || b[i] == 0) last_kill = (int64_t)i;
+        if (b[i] == '\n') last_lf = (int64_t)i;
+    }
+    return stop;
+}
+
+/* ------------------------------------------------------------------------- */
+/* What main.cu prints: main.cu:166,180,210-218                                */
+/* ------------------------------------------------------------------------- */
+
+typedef struct { char *buf; size_t cap, len; } sbuf;
+static void sb_put(sbuf *s, const void *p, size_t n) {
+    if (s->len + n <= s->cap) memcpy(s->buf + s->len, p, n);
+    s->len += n;
+}
+
+size_t orc_render_stdout(const uint8_t *data, size_t n, int linecap, int file_present,
+                         const orc_result *r, char *buf, size_t cap) {
+    sbuf s = {buf, cap, 0};
+    static const char sep[] = "--------------------------\n";
+    sb_put(&s, "Input Data:\n", 12); /* main.cu:166 */
+    if (file_present) {
+        orc_chunk c = {0, 0, 0};
+        for (;;) {
+            int got = next_chunk(data, n, linecap, &c);
+            if (got) sb_put(&s, data + c.pos, c.slen); /* printf("%s", szLine), main.cu:180 */
+            if (!got || c.slen < 2) break;
+        }
+    }
+    sb_put(&s, sep, sizeof(sep) - 1); /* main.cu:210 */
+    char num[48];
+    for (size_t i = 0; i < r->n_rows; i++) { /* main.cu:212-215 */
+        sb_put(&s, data + r->rows[i].off, r->rows[i].len);
+        int k = snprintf(num, sizeof(num), "\t%lld\n", (long long)r->rows[i].count);
+        sb_put(&s, num, (size_t)k);
+    }
+    sb_put(&s, sep, sizeof(sep) - 1); /* main.cu:217 */
+    int k = snprintf(num, sizeof(num), "Total Count:%lld\n", (long long)r->total);
+    sb_put(&s, num, (size_t)k); /* main.cu:218 */
+    return s.len;
+}

@@ -1,0 +1,83 @@
+/*
+ * oracle/ -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * A CPU restatement of the word-count path of zimisoho/cuda-mapreduce
+ * (/root/reference/main.cu).  Only tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py may use it, and only as
+ * the checker or as the timed CPU baseline.  The product (libwc.so) never
+ * links or calls anything in this directory.
+ *
+ * Parity status: PINNED.  orc_literal() is checked against the reference's own
+ * unmodified source executed on host cores (oracle/_ref/main_cpu, built by
+ * oracle/Makefile from /root/reference/main.cu) on the bundled test.txt, on the
+ * quirk vectors of SURVEY.md App. C.2 and under fuzzing; the outputs are
+ * committed under tests/golden/.  orc_fast() is checked against orc_literal().
+ */
+#ifndef WC_ORACLE_H
+#define WC_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORC_LINECAP_REF 99 /* fgets(szLine, 100, ...)  main.cu:175,179 */
+#define ORC_LINECAP_INF 0  /* capacity lifted: one chunk == one whole line */
+
+#define ORC_MODE_REF 0   /* first-match-by-prefix reduce, main.cu:57-67,81-89 */
+#define ORC_MODE_EXACT 1 /* plain equality counts (no prefix merge, empties dropped) */
+
+typedef struct orc_row {
+    uint64_t off;   /* byte offset in the input of one occurrence of the word */
+    uint32_t len;   /* word length in bytes */
+    int64_t count;  /* what the reference would print after the tab */
+    uint64_t first; /* offset of the delimiter that flushed the first occurrence */
+} orc_row;
+
+typedef struct orc_result {
+    orc_row *rows; /* in output (insertion) order, main.cu:212-215 */
+    size_t n_rows;
+    int64_t total;         /* "Total Count", main.cu:214,218 */
+    uint64_t n_flush;      /* words emitted by the splitter, empty ones included */
+    uint64_t n_empty;      /* of which empty (main.cu:190-194 on a delimiter run) */
+    uint64_t n_lost_empty; /* empties seen before the first non-empty word (S13) */
+    uint64_t stop;         /* offset where input processing ended (== n if it ran out) */
+    uint64_t n_chunks;     /* fgets chunks that were split into words */
+    uint64_t n_cr;         /* 0x0D bytes seen inside processed chunks */
+    uint64_t n_nul;        /* 0x00 bytes seen inside processed chunks */
+    uint64_t max_line;     /* longest line (bytes, newline included) */
+} orc_result;
+
+/* Verbatim restatement: splitter main.cu:174-206, mapper 37-54, compare 57-67,
+ * reducer 69-108, with the fixed capacities lifted.  O(words x rows). */
+int orc_literal(const uint8_t *data, size_t n, int linecap, orc_result *out);
+
+/* Same results through exact counts + first occurrence + the order-free
+ * post-pass.  linecap is always ORC_LINECAP_INF here. */
+int orc_fast(const uint8_t *data, size_t n, int mode, orc_result *out);
+
+/* orc_fast over `nthreads` line-aligned slices, merged.  Same results. */
+int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_result *out);
+
+void orc_free(orc_result *r);
+
+/* The byte-parallel statement of the splitter: for every byte
+ * writes 1 into flush[i] iff byte i emits a word; returns STOP.  Used to test
+ * that the formula the GPU kernels implement equals the line-by-line code. */
+uint64_t orc_flush_formula(const uint8_t *data, size_t n, uint8_t *flush);
+
+/* The same marks produced by the line-by-line splitter (main.cu:174-206). */
+uint64_t orc_split_flushes(const uint8_t *data, size_t n, int linecap, uint8_t *flush);
+
+/* Renders what main.cu prints (main.cu:166,180,210-218): header, echo of every
+ * chunk read, separator, rows, separator, total.  Returns bytes written (or
+ * needed, if cap is too small). */
+size_t orc_render_stdout(const uint8_t *data, size_t n, int linecap, int file_present,
+                         const orc_result *r, char *buf, size_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

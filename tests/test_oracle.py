@@ -1,0 +1,152 @@
+"""CPU tests that pin the oracle (oracle/) to the reference.
+
+Chain: reference's own main.cu on host cores (golden
+fixtures, and live where oracle/_ref/main_cpu exists) == orc_literal(linecap 99)
+== orc_literal(lifted) on short lines == orc_fast == orc_fast_mt, and the
+byte-parallel flush formula == the line-by-line splitter.
+"""
+import os
+import random
+import tempfile
+
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from oracle import orc as O
+
+ALPHABET = [b"a", b"b", b"ab", b"abc", b"abcd", b"A", b"a,", b"the", b"then", b"x", b"longerword9",
+            b"averyveryverylongword_over_16", b"\t", b"\xc3\xa9"]
+DELIMS = [b" ", b" ", b" ", b"\n", b"\n", b"\r\n", b"  ", b"\r", b"\0", b"\n\n"]
+
+
+def random_text(rng, n_tokens, weird=0.15):
+    out = bytearray()
+    for _ in range(n_tokens):
+        out += rng.choice(ALPHABET)
+        if rng.random() < weird:
+            out += rng.choice(DELIMS)
+        else:
+            out += rng.choice([b" ", b" ", b" ", b"\n"])
+    if rng.random() < 0.3:
+        out += rng.choice(ALPHABET)
+    return bytes(out)
+
+
+def test_golden_literal_matches_reference(golden):
+    for name, data, expect in golden:
+        if data is None:
+            got = O.render_missing_file()
+        else:
+            got = O.literal(data, O.LINECAP_REF, render=True).stdout
+        assert got == expect, name
+
+
+def test_survey_c2_known_answers():
+    # SURVEY.md App. C.2 rows, as (input, rows, total)
+    table = [
+        (b"Hello He He\n", [(b"Hello", 3)], 3),
+        (b"He Hello He\n", [(b"He", 2), (b"Hello", 1)], 3),
+        (b"a  b a\n", [(b"a", 3), (b"b", 1)], 4),
+        (b"  a b\n", [(b"a", 1), (b"b", 1)], 2),
+        (b"a b \n", [(b"a", 2), (b"b", 1)], 3),
+        (b"a b\nc d", [(b"a", 1), (b"b", 1), (b"c", 1)], 3),
+        (b"a b\r\nc d\r\n", [(b"a", 1), (b"b", 1), (b"c", 1), (b"d", 1)], 4),
+        (b"a\tb c\n", [(b"a\tb", 1), (b"c", 1)], 2),
+        (b"a b\n\nc d\n", [(b"a", 1), (b"b", 1)], 2),
+        (b"a b\nc", [(b"a", 1), (b"b", 1)], 2),
+        (b"a, a a. a\n", [(b"a,", 3), (b"a.", 1)], 4),
+        (b"a\rb c\nd\n", [(b"a", 1), (b"d", 1)], 2),
+        (b"ab\0cd ef\ngh\n", [(b"gh", 1)], 1),
+        (b" \n \n", [], 0),
+    ]
+    for data, rows, total in table:
+        for r in (O.literal(data, O.LINECAP_REF), O.literal(data, O.LINECAP_INF), O.fast(data)):
+            assert r.pairs() == rows, data
+            assert r.total == total, data
+
+
+def test_test_txt_known_answer(golden):
+    data = dict((n, d) for n, d, _ in golden)["test_txt"]
+    r = O.fast(data)
+    assert r.pairs() == [(b"Hello", 2), (b"World", 2), (b"EveryOne", 1), (b"Good", 2), (b"News", 1),
+                         (b"Morning", 1)]
+    assert r.total == 9 and r.n_flush == 9 and r.n_empty == 0 and r.stop == len(data)
+
+
+def check_chain(data):
+    lit = O.literal(data, O.LINECAP_INF)
+    fast = O.fast(data)
+    assert fast.pairs() == lit.pairs()
+    assert fast.total == lit.total
+    assert (fast.n_flush, fast.n_empty, fast.n_lost_empty, fast.stop) == \
+           (lit.n_flush, lit.n_empty, lit.n_lost_empty, lit.stop)
+    assert [f for _, _, f in fast.rows] == [f for _, _, f in lit.rows]
+    if lit.max_line <= 99:  # chunking never splits a line: literal == lifted (App. A.2 L5)
+        cap = O.literal(data, O.LINECAP_REF)
+        assert cap.pairs() == lit.pairs() and cap.total == lit.total
+    stop_f, marks_f = O.flush_formula(data)
+    stop_s, marks_s = O.split_flushes(data)
+    assert stop_f == stop_s == lit.stop
+    assert marks_f == marks_s
+    assert sum(marks_s) == lit.n_flush
+    # exact mode: plain equality counts of non-empty words
+    ex = O.fast(data, O.MODE_EXACT)
+    assert ex.total == lit.n_flush - lit.n_empty
+    return lit
+
+
+def test_chain_on_golden_inputs(golden):
+    for name, data, _ in golden:
+        if data is not None:
+            check_chain(data)
+
+
+def test_chain_fuzz_seeded():
+    rng = random.Random(1234)
+    nontrivial = 0
+    for _ in range(400):
+        data = random_text(rng, rng.randint(0, 120), weird=rng.choice([0.0, 0.1, 0.4]))
+        lit = check_chain(data)
+        ex = O.fast(data, O.MODE_EXACT)
+        nontrivial += ex.pairs() != lit.pairs()
+    assert nontrivial > 100  # the prefix rule must actually bite in this corpus
+
+
+@settings(max_examples=300, deadline=None)
+@given(st.lists(st.sampled_from(ALPHABET + DELIMS), max_size=200))
+def test_chain_hypothesis(tokens):
+    check_chain(b"".join(tokens))
+
+
+@settings(max_examples=200, deadline=None)
+@given(st.binary(max_size=300))
+def test_chain_arbitrary_bytes(data):
+    check_chain(data)
+
+
+def test_fast_mt_equals_fast():
+    rng = random.Random(99)
+    for trial in range(6):
+        weird = [0.0, 0.0, 0.02, 0.0, 0.1, 0.0][trial]
+        data = random_text(rng, 60000, weird=weird)
+        if trial == 3:  # a blank line in the middle stops every later slice
+            data = data[:len(data) // 2] + b"\n\n" + data[len(data) // 2:]
+        a = O.fast(data)
+        for nt in (2, 3, 8):
+            b = O.fast_mt(data, nthreads=nt)
+            assert b.pairs() == a.pairs() and b.total == a.total
+            assert (b.n_flush, b.n_empty, b.n_lost_empty, b.stop) == (a.n_flush, a.n_empty, a.n_lost_empty, a.stop)
+
+
+@pytest.mark.skipif(not os.path.exists(O.REF_CPU), reason="oracle/_ref/main_cpu not built (no /root/reference)")
+def test_live_reference_fuzz():
+    """orc_literal vs the reference's own code, on fresh inputs inside main.cu's capacities."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "make_golden", os.path.join(os.path.dirname(__file__), "golden", "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    with tempfile.TemporaryDirectory() as td:
+        for name, data in mg.fuzz_vectors(150, 777):
+            ref = O.run_reference_cpu(data, td)
+            assert O.literal(data, O.LINECAP_REF, render=True).stdout == ref, (name, data)
