@@ -1,0 +1,10 @@
+"""cuda-mapreduce_b200: B200-native word count behind the program surface of zimisoho/cuda-mapreduce.
+
+The product is the C-ABI library `libwc.so` (include/wc.h) and the `wordcount` CLI, both built from
+csrc/ for sm_100a.  This Python package is a thin ctypes view of that ABI for the tests and bench.py;
+it contains no computation.  There is no CPU path: every counting call needs the CUDA library and a
+B200, and fails loudly otherwise.
+"""
+from .wc import (  # noqa: F401
+    MODE_EXACT, MODE_REF, Config, Engine, WcError, build, declared_symbols, lib, lib_path, run_map_reduce,
+)

@@ -1,0 +1,460 @@
+// wc_engine.cu -- host side of libwc.so: the C ABI of include/wc.h over the kernels of
+// wc_device.cuh.  Replaces the reference's driver runMapReduce() (/root/reference/main.cu:133-162:
+// cudaMalloc / blocking cudaMemcpy / two <<<100,100>>> launches / cudaFree, with no error checks)
+// by an engine that keeps its device tables alive, streams host text through pinned, double-buffered
+// cudaMemcpyAsync chunks, and checks every CUDA call.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/wc.h"
+#include "wc_device.cuh"
+#include "wc_finalize.h"
+
+using wc::u32;
+using wc::u64;
+
+struct wc_engine {
+    wc_config cfg{};
+    int device = 0;
+    int num_sms = 0;
+    int grid = 0;
+    cudaStream_t stream = nullptr;      // kernels
+    cudaStream_t copy_stream = nullptr; // host -> device chunks
+    std::string err;
+
+    // device tables: one allocation, so that a reset is a single memset
+    void *table_block = nullptr;
+    size_t table_block_bytes = 0;
+    wc::Tables T{};
+    wc::Status *d_status = nullptr;
+    wc::WarpSummary *d_ws = nullptr;
+    u32 n_ws = 0;
+    wc::Status *h_status = nullptr; // pinned
+
+    // streaming (allocated on first wc_feed)
+    size_t chunk_cap = 0;
+    uint8_t *d_chunk[2] = {nullptr, nullptr};
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_counted[2] = {nullptr, nullptr};
+    int ring = 0;
+    std::vector<uint8_t> carry; // bytes after the last '\n' seen so far (an unfinished line)
+
+    u64 consumed = 0; // bytes handed to the device so far
+    u64 fed = 0;      // bytes given to wc_feed / wc_count_device
+    u64 launches = 0;
+    u64 grows = 0;
+
+    // timing: one event pair per piece
+    std::vector<cudaEvent_t> ev_pool;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_used;
+    double device_ms = 0;
+};
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t ck_e = (call);                                                                       \
+        if (ck_e != cudaSuccess) {                                                                       \
+            e->err = std::string(#call) + ": " + cudaGetErrorString(ck_e);                              \
+            return ck_e == cudaErrorMemoryAllocation ? WC_ERR_NOMEM : WC_ERR_CUDA;                       \
+        }                                                                                                \
+    } while (0)
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ----------------------------------------------------------------- tables
+
+static int alloc_tables(wc_engine *e, u32 s_log2, u32 l_log2, u64 arena_bytes, wc::Tables *out, void **block,
+                        size_t *block_bytes) {
+    const size_t s_n = (size_t)1 << s_log2, l_n = (size_t)1 << l_log2;
+    const size_t bytes = (3 * s_n + 3 * l_n) * sizeof(u64);
+    void *p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    u64 *q = (u64 *)p;
+    wc::Tables T = e->T;
+    T.s_keys = q; T.s_counts = q + s_n; T.s_finv = q + 2 * s_n;
+    q += 3 * s_n;
+    T.l_refs = q; T.l_counts = q + l_n; T.l_finv = q + 2 * l_n;
+    T.s_log2 = s_log2; T.l_log2 = l_log2;
+    if (T.arena == nullptr) {
+        const u64 units = arena_bytes / 8;
+        CK(cudaMalloc((void **)&T.arena, units * 8));
+        T.arena_units = units;
+    }
+    *out = T; *block = p; *block_bytes = bytes;
+    return WC_OK;
+}
+
+static int reset_device_state(wc_engine *e) {
+    CK(cudaMemsetAsync(e->table_block, 0, e->table_block_bytes, e->stream));
+    wc::Status s;
+    memset(&s, 0, sizeof(s));
+    s.stop = wc::kNone; s.p0 = wc::kNone; s.arena_used = 1;
+    *e->h_status = s;
+    CK(cudaMemcpyAsync(e->d_status, e->h_status, sizeof(s), cudaMemcpyHostToDevice, e->stream));
+    return WC_OK;
+}
+
+// ----------------------------------------------------------------- C ABI
+
+extern "C" {
+
+void wc_config_default(wc_config *cfg) {
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->struct_size = (uint32_t)sizeof(*cfg);
+    cfg->device = 0;
+    cfg->mode = WC_MODE_REF;
+    cfg->path = WC_PATH_AUTO;
+    cfg->chunk_bytes = 64ull << 20;
+    cfg->short_table_log2 = 21;
+    cfg->long_table_log2 = 21;
+    cfg->arena_bytes = 256ull << 20;
+}
+
+static thread_local std::string g_create_err; // why the last wc_create on this thread failed
+
+const char *wc_last_error(const wc_engine *e) { return e ? e->err.c_str() : g_create_err.c_str(); }
+
+void wc_destroy(wc_engine *e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
+    for (auto ev : e->ev_pool) cudaEventDestroy(ev);
+    for (auto &p : e->ev_used) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    for (int i = 0; i < 2; i++) {
+        if (e->d_chunk[i]) cudaFree(e->d_chunk[i]);
+        if (e->ev_copied[i]) cudaEventDestroy(e->ev_copied[i]);
+        if (e->ev_counted[i]) cudaEventDestroy(e->ev_counted[i]);
+    }
+    if (e->table_block) cudaFree(e->table_block);
+    if (e->T.arena) cudaFree(e->T.arena);
+    if (e->d_status) cudaFree(e->d_status);
+    if (e->d_ws) cudaFree(e->d_ws);
+    if (e->h_status) cudaFreeHost(e->h_status);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    delete e;
+}
+
+static int create_impl(wc_engine *e, const wc_config *cfg) {
+    wc_config_default(&e->cfg);
+    if (cfg) {
+        if (cfg->struct_size != sizeof(wc_config)) { e->err = "wc_config.struct_size mismatch"; return WC_ERR_INVALID; }
+        e->cfg = *cfg;
+    }
+    wc_config &c = e->cfg;
+    if (c.chunk_bytes == 0) c.chunk_bytes = 64ull << 20;
+    if (c.short_table_log2 == 0) c.short_table_log2 = 21;
+    if (c.long_table_log2 == 0) c.long_table_log2 = 21;
+    if (c.arena_bytes == 0) c.arena_bytes = 256ull << 20;
+    if (c.short_table_log2 < 10 || c.short_table_log2 > 34 || c.long_table_log2 < 10 || c.long_table_log2 > 34 ||
+        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT)) {
+        e->err = "wc_config out of range";
+        return WC_ERR_INVALID;
+    }
+    c.chunk_bytes = align_up(c.chunk_bytes, 4096);
+    e->device = c.device;
+    CK(cudaSetDevice(e->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, e->device));
+    if (prop.major < 10) { e->err = "libwc.so needs an sm_100a GPU (B200)"; return WC_ERR_CUDA; }
+    e->num_sms = prop.multiProcessorCount;
+    e->grid = e->num_sms; // persistent: one CTA per SM, the shared-memory table fills the SM
+    CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+    CK(cudaFuncSetAttribute(wc::count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::kSmemTotal));
+    CK(cudaMalloc((void **)&e->d_status, sizeof(wc::Status)));
+    CK(cudaMallocHost((void **)&e->h_status, sizeof(wc::Status)));
+    e->T.st = e->d_status;
+    e->n_ws = (u32)e->grid * wc::kWarps;
+    CK(cudaMalloc((void **)&e->d_ws, sizeof(wc::WarpSummary) * e->n_ws));
+    int rc = alloc_tables(e, c.short_table_log2, c.long_table_log2, c.arena_bytes, &e->T, &e->table_block,
+                          &e->table_block_bytes);
+    if (rc != WC_OK) return rc;
+    rc = reset_device_state(e);
+    if (rc != WC_OK) return rc;
+    CK(cudaStreamSynchronize(e->stream));
+    return WC_OK;
+}
+
+int wc_create(wc_engine **out, const wc_config *cfg) {
+    if (!out) return WC_ERR_INVALID;
+    *out = nullptr;
+    wc_engine *e = new (std::nothrow) wc_engine();
+    if (!e) return WC_ERR_NOMEM;
+    int rc = create_impl(e, cfg);
+    if (rc != WC_OK) {
+        g_create_err = e->err;
+        wc_destroy(e);
+        return rc;
+    }
+    *out = e;
+    return WC_OK;
+}
+
+int wc_reset(wc_engine *e) {
+    if (!e) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->copy_stream));
+    int rc = reset_device_state(e);
+    if (rc != WC_OK) return rc;
+    e->carry.clear();
+    e->consumed = 0; e->fed = 0; e->launches = 0; e->device_ms = 0;
+    for (auto &p : e->ev_used) { e->ev_pool.push_back(p.first); e->ev_pool.push_back(p.second); }
+    e->ev_used.clear();
+    return WC_OK;
+}
+
+} // extern "C"
+
+// Launches the forward count of one piece and its roll-back/summary companion on e->stream.
+static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
+    if (n == 0) return WC_OK;
+    const u64 tiles = (n + wc::kTile - 1) / wc::kTile;
+    const u64 warps = (u64)e->grid * wc::kWarps;
+    const u64 tpw = (tiles + warps - 1) / warps;
+    if (tpw * wc::kWarps * wc::kTile >= 0xFFFFFFF0ull) { e->err = "piece too large for one launch"; return WC_ERR_TOO_LARGE; }
+    wc::Launch L;
+    L.buf = dev; L.n = n; L.base = e->cfg.base_offset + e->consumed;
+    L.tiles_per_warp = (u32)tpw; L.last_piece = last_piece; L.negate = 0;
+    L.ws = e->d_ws; L.n_ws = e->n_ws;
+
+    cudaEvent_t a, b;
+    for (cudaEvent_t *ev : {&a, &b}) {
+        if (!e->ev_pool.empty()) { *ev = e->ev_pool.back(); e->ev_pool.pop_back(); }
+        else CK(cudaEventCreate(ev));
+    }
+    CK(cudaEventRecord(a, e->stream));
+    wc::count_kernel<<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+    L.negate = 1;
+    wc::count_kernel<<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(b, e->stream));
+    e->ev_used.emplace_back(a, b);
+    e->consumed += n;
+    e->launches += 2;
+    return WC_OK;
+}
+
+static int ensure_chunks(wc_engine *e) {
+    if (e->d_chunk[0]) return WC_OK;
+    e->chunk_cap = e->cfg.chunk_bytes;
+    for (int i = 0; i < 2; i++) {
+        CK(cudaMalloc((void **)&e->d_chunk[i], e->chunk_cap + 64));
+        CK(cudaEventCreateWithFlags(&e->ev_copied[i], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&e->ev_counted[i], cudaEventDisableTiming));
+        CK(cudaEventRecord(e->ev_counted[i], e->stream));
+    }
+    return WC_OK;
+}
+
+// One piece (whole lines, or the end of the input) from host memory through the chunk ring.
+static int feed_piece(wc_engine *e, const uint8_t *src, size_t n, int last_piece) {
+    if (n == 0) return WC_OK;
+    int rc = ensure_chunks(e);
+    if (rc != WC_OK) return rc;
+    if (n <= e->chunk_cap) {
+        const int s = e->ring;
+        CK(cudaStreamWaitEvent(e->copy_stream, e->ev_counted[s], 0)); // the kernel that read this buffer is done
+        CK(cudaMemcpyAsync(e->d_chunk[s], src, n, cudaMemcpyHostToDevice, e->copy_stream));
+        CK(cudaEventRecord(e->ev_copied[s], e->copy_stream));
+        CK(cudaStreamWaitEvent(e->stream, e->ev_copied[s], 0));
+        rc = launch_piece(e, e->d_chunk[s], n, last_piece);
+        if (rc != WC_OK) return rc;
+        CK(cudaEventRecord(e->ev_counted[s], e->stream));
+        e->ring ^= 1;
+        return WC_OK;
+    }
+    // a single line longer than the chunk: give it a buffer of its own
+    uint8_t *tmp = nullptr;
+    CK(cudaMallocAsync((void **)&tmp, n + 64, e->stream));
+    CK(cudaMemcpyAsync(tmp, src, n, cudaMemcpyHostToDevice, e->stream));
+    rc = launch_piece(e, tmp, n, last_piece);
+    if (rc != WC_OK) return rc;
+    CK(cudaFreeAsync(tmp, e->stream));
+    CK(cudaStreamSynchronize(e->stream)); // src must stay valid until the copy has run
+    return WC_OK;
+}
+
+extern "C" {
+
+int wc_feed(wc_engine *e, const void *bytes, size_t n) {
+    if (!e || (!bytes && n)) return WC_ERR_INVALID;
+    if (n == 0) return WC_OK;
+    CK(cudaSetDevice(e->device));
+    const uint8_t *p = (const uint8_t *)bytes;
+    size_t left = n;
+    e->fed += n;
+    int rc = WC_OK;
+
+    // finish the line left over from the previous call
+    if (!e->carry.empty()) {
+        const uint8_t *nl = (const uint8_t *)memchr(p, '\n', left);
+        const size_t take = nl ? (size_t)(nl - p) + 1 : left;
+        e->carry.insert(e->carry.end(), p, p + take);
+        p += take; left -= take;
+        if (!nl) return WC_OK;
+        rc = feed_piece(e, e->carry.data(), e->carry.size(), 0);
+        if (rc != WC_OK) return rc;
+        CK(cudaStreamSynchronize(e->copy_stream)); // carry is about to be reused
+        e->carry.clear();
+    }
+    // whole-line pieces straight from the caller's buffer
+    while (left > 0) {
+        const size_t take = left < e->cfg.chunk_bytes ? left : (size_t)e->cfg.chunk_bytes;
+        const uint8_t *nl = (const uint8_t *)memrchr(p, '\n', take);
+        size_t piece;
+        if (nl) piece = (size_t)(nl - p) + 1;
+        else {
+            const uint8_t *fw = take < left ? (const uint8_t *)memchr(p + take, '\n', left - take) : nullptr;
+            if (!fw) break; // no line end in what is left: keep it for the next call
+            piece = (size_t)(fw - p) + 1;
+        }
+        rc = feed_piece(e, p, piece, 0);
+        if (rc != WC_OK) return rc;
+        p += piece; left -= piece;
+    }
+    if (left > 0) e->carry.insert(e->carry.end(), p, p + left);
+    CK(cudaStreamSynchronize(e->copy_stream)); // the caller may reuse `bytes` now
+    return WC_OK;
+}
+
+int wc_count_device(wc_engine *e, const void *dev_bytes, size_t n, int last_piece) {
+    if (!e || (!dev_bytes && n)) return WC_ERR_INVALID;
+    if (!e->carry.empty()) { e->err = "wc_count_device after an unfinished wc_feed line"; return WC_ERR_INVALID; }
+    if (((uintptr_t)dev_bytes & 15) != 0) { e->err = "device buffer must be 16-byte aligned"; return WC_ERR_UNALIGNED; }
+    CK(cudaSetDevice(e->device));
+    e->fed += n;
+    return launch_piece(e, (const uint8_t *)dev_bytes, n, last_piece);
+}
+
+int wc_sync(wc_engine *e) {
+    if (!e) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->copy_stream));
+    CK(cudaStreamSynchronize(e->stream));
+    for (auto &p : e->ev_used) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, p.first, p.second));
+        e->device_ms += ms;
+        e->ev_pool.push_back(p.first); e->ev_pool.push_back(p.second);
+    }
+    e->ev_used.clear();
+    return WC_OK;
+}
+
+int wc_device_ms(wc_engine *e, double *ms, uint64_t *kernel_launches) {
+    if (!e) return WC_ERR_INVALID;
+    if (ms) *ms = e->device_ms;
+    if (kernel_launches) *kernel_launches = e->launches;
+    return WC_OK;
+}
+
+void *wc_stream(wc_engine *e) { return e ? (void *)e->stream : nullptr; }
+
+int wc_host_alloc(void **p, size_t n) {
+    if (!p) return WC_ERR_INVALID;
+    return cudaMallocHost(p, n ? n : 1) == cudaSuccess ? WC_OK : WC_ERR_NOMEM;
+}
+
+int wc_host_free(void *p) { return cudaFreeHost(p) == cudaSuccess ? WC_OK : WC_ERR_CUDA; }
+
+int wc_finish(wc_engine *e, wc_result **out) {
+    if (!e || !out) return WC_ERR_INVALID;
+    *out = nullptr;
+    CK(cudaSetDevice(e->device));
+    int rc;
+    if (!e->carry.empty()) { // the unterminated end of the input (main.cu:198-203 drops its last word)
+        rc = feed_piece(e, e->carry.data(), e->carry.size(), 1);
+        if (rc != WC_OK) return rc;
+    }
+    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+    rc = wc_sync(e);
+    if (rc != WC_OK) return rc;
+    e->carry.clear();
+    const wc::Status st = *e->h_status;
+    if (st.err) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "device tables full (flags 0x%x: short=%llu long=%llu arena=%llu units)", st.err,
+                 (unsigned long long)st.s_entries, (unsigned long long)st.l_entries, (unsigned long long)st.arena_used);
+        e->err = msg;
+        return WC_ERR_TABLE_FULL;
+    }
+
+    // ---- bring the tables to the host
+    const size_t s_n = (size_t)1 << e->T.s_log2, l_n = (size_t)1 << e->T.l_log2;
+    std::vector<u64> tab((3 * s_n + 3 * l_n));
+    CK(cudaMemcpyAsync(tab.data(), e->table_block, tab.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    std::vector<u64> arena((size_t)st.arena_used);
+    if (st.arena_used > 1)
+        CK(cudaMemcpyAsync(arena.data(), e->T.arena, arena.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+
+    const u64 *s_keys = tab.data(), *s_counts = s_keys + s_n, *s_finv = s_keys + 2 * s_n;
+    const u64 *l_refs = tab.data() + 3 * s_n, *l_counts = l_refs + l_n, *l_finv = l_refs + 2 * l_n;
+    std::string blob;
+    std::vector<wc::HostEntry> entries;
+    entries.reserve((size_t)(st.s_entries + st.l_entries));
+    for (size_t i = 0; i < s_n; i++) {
+        const u64 k = s_keys[i];
+        if (k == 0 || (int64_t)s_counts[i] == 0) continue;
+        u32 len = 8;
+        while (len > 1 && ((k >> (8 * (len - 1))) & 0xFF) == 0) len--;
+        entries.push_back(wc::HostEntry{blob.size(), len, (int64_t)s_counts[i], ~s_finv[i]});
+        blob.append((const char *)&k, len);
+    }
+    for (size_t i = 0; i < l_n; i++) {
+        const u64 r = l_refs[i];
+        if (r == 0 || (int64_t)l_counts[i] == 0) continue;
+        const u64 unit = r & ((1ull << 40) - 1);
+        const u64 len = arena[unit];
+        entries.push_back(wc::HostEntry{blob.size(), (u32)len, (int64_t)l_counts[i], ~l_finv[i]});
+        blob.append((const char *)&arena[unit + 1], (size_t)len);
+    }
+
+    wc_result *r = new (std::nothrow) wc_result();
+    if (!r) return WC_ERR_NOMEM;
+    const u64 total_bytes = e->consumed;
+    const u64 stop_abs = st.stop == wc::kNone ? e->cfg.base_offset + total_bytes : st.stop;
+    u64 lost = st.lost_empty;
+    if (!st.p0_found || st.p0 >= stop_abs) lost = st.n_empty; // no non-empty word at all: every empty one is lost
+    r->stats.bytes = total_bytes;
+    r->stats.n_flush = st.n_flush;
+    r->stats.n_empty = st.n_empty;
+    r->stats.n_lost_empty = lost;
+    r->stats.stop = stop_abs - e->cfg.base_offset;
+    r->stats.n_distinct = entries.size();
+    r->stats.n_long_words = st.n_long;
+    r->stats.n_spilled = st.n_spill;
+    r->stats.n_slow_tiles = st.n_slow_tiles;
+    r->stats.table_grows = e->grows;
+    r->stats.device_ms = e->device_ms;
+    wc::finalize_rows(std::move(blob), entries, e->cfg.mode, st.n_empty, lost, r);
+    *out = r;
+    return WC_OK;
+}
+
+} // extern "C"
+
+// Test hook (no GPU needed): the SWAR byte classification and flag->mask compaction of the
+// tokenizer kernel, run on the host from the same source (classify4 / movemask16 in wc_device.cuh).
+extern "C" int wc_debug_classify16(const uint8_t *bytes16, uint32_t *delim_mask, uint32_t *lf_mask,
+                                   uint32_t *kill_mask) {
+    if (!bytes16 || !delim_mask || !lf_mask || !kill_mask) return WC_ERR_INVALID;
+    u32 w[4];
+    memcpy(w, bytes16, 16);
+    wc::ByteFlags f0 = wc::classify4(w[0]), f1 = wc::classify4(w[1]), f2 = wc::classify4(w[2]), f3 = wc::classify4(w[3]);
+    *delim_mask = wc::movemask16(f0.delim, f1.delim, f2.delim, f3.delim);
+    *lf_mask = wc::movemask16(f0.lf, f1.lf, f2.lf, f3.lf);
+    *kill_mask = wc::movemask16(f0.kill, f1.kill, f2.kill, f3.kill);
+    return WC_OK;
+}
+
+extern "C" uint32_t wc_debug_smem_slot(uint64_t key) {
+    return (uint32_t)(((uint64_t)wc::hash32((u32)key, (u32)(key >> 32)) * wc::kSmemEntries) >> 32);
+}

@@ -1,0 +1,43 @@
+// wc_finalize.h -- host side of the reduce: turns the device tables' exact counts into the rows
+// the reference prints.  Pure C++ (no CUDA), so the CPU tests can drive it.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/wc.h"
+
+namespace wc {
+
+struct HostEntry {      // one distinct non-empty word with its exact count
+    uint64_t blob_off;  // where its bytes start in the blob
+    uint32_t len;
+    int64_t count;
+    uint64_t first;     // offset of the delimiter that flushed its first occurrence
+};
+
+struct Row {
+    uint64_t blob_off;
+    uint32_t len;
+    int64_t count;
+    uint64_t first;
+};
+
+} // namespace wc
+
+struct wc_result {
+    std::string blob; // bytes of every row's word
+    std::vector<wc::Row> rows;
+    int64_t total = 0;
+    wc_stats stats{};
+};
+
+namespace wc {
+
+// Applies the reduce semantics of /root/reference/main.cu:57-108 in its order-free form
+// (SURVEY.md A.3).  `entries` index into `blob`; the result takes ownership of `blob`.
+void finalize_rows(std::string &&blob, std::vector<HostEntry> &entries, int mode, uint64_t n_empty,
+                   uint64_t n_lost_empty, wc_result *out);
+
+} // namespace wc

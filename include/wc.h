@@ -1,0 +1,161 @@
+/*
+ * wc.h -- C ABI of libwc.so, a B200-native (sm_100a) word-count engine that is a
+ * drop-in for the tokenize -> count path of zimisoho/cuda-mapreduce.
+ *
+ * What it replaces in the reference (all in /root/reference/main.cu):
+ *   - the host splitter                         main.cu:174-206
+ *   - mapper / mapKernel / cudaMap              main.cu:37-54, 109-117, 124-127
+ *   - compare / reducer / reduceKernel / cudaReduce   main.cu:57-108, 119-123, 129-132
+ *   - the driver runMapReduce()                 main.cu:133-162
+ * The engine reads raw text bytes and produces the rows the reference prints
+ * (main.cu:210-218), bit for bit, with the reference's fixed capacities
+ * (main.cu:9-15) lifted.  Semantics: SURVEY.md Appendix A.
+ *
+ * Conventions: plain pointers and sizes, no C++ or torch types.  Every call
+ * returns 0 (WC_OK) or a negative wc_status; nothing prints or exits.  The
+ * engine owns all device and pinned memory it allocates; a wc_result owns the
+ * host memory its accessors point into.  One engine is used by one host
+ * thread at a time.  Counts and offsets are 64-bit.
+ */
+#ifndef WC_H
+#define WC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define WC_API __attribute__((visibility("default")))
+#else
+#define WC_API
+#endif
+
+typedef struct wc_engine wc_engine;
+typedef struct wc_result wc_result;
+
+typedef enum wc_status {
+    WC_OK = 0,
+    WC_ERR_INVALID = -1,    /* bad argument / call order */
+    WC_ERR_CUDA = -2,       /* a CUDA runtime call failed (wc_last_error has the text) */
+    WC_ERR_NOMEM = -3,      /* host or device allocation failed */
+    WC_ERR_TABLE_FULL = -4, /* a device table or the long-word arena could not grow further */
+    WC_ERR_UNALIGNED = -5,  /* device buffer not 16-byte aligned */
+    WC_ERR_NCCL = -6,
+    WC_ERR_TOO_LARGE = -7   /* size beyond what this entry point supports */
+} wc_status;
+
+/* Reduce semantics. */
+#define WC_MODE_REF 0   /* main.cu's reducer: first match by PREFIX in insertion order (main.cu:57-67,
+                           81-89), empty words credited to row 0 (main.cu:81,103)  */
+#define WC_MODE_EXACT 1 /* plain equality counts of non-empty words */
+
+/* Aggregation path (wc_config.path). */
+#define WC_PATH_AUTO 0
+#define WC_PATH_HASH 1 /* shared-memory table spilling to a global open-addressing table */
+#define WC_PATH_SORT 2 /* radix sort of (hash, offset, length) + segmented reduce */
+
+typedef struct wc_config {
+    uint32_t struct_size;      /* = sizeof(wc_config) */
+    int32_t device;            /* CUDA device ordinal */
+    int32_t mode;              /* WC_MODE_* */
+    int32_t path;              /* WC_PATH_* */
+    uint64_t chunk_bytes;      /* wc_feed() streaming chunk (0: 64 MiB) */
+    uint32_t short_table_log2; /* global table slots for words <= 8 bytes (0: 2^21) */
+    uint32_t long_table_log2;  /* global table slots for longer words (0: 2^21) */
+    uint64_t arena_bytes;      /* device byte store for longer words (0: 256 MiB) */
+    uint64_t base_offset;      /* offset of this engine's first byte in the whole input (shards) */
+    uint32_t flags;            /* reserved, 0 */
+    uint32_t reserved;
+} wc_config;
+
+/* Counters of one finished job; the same numbers the oracle reports. */
+typedef struct wc_stats {
+    uint64_t bytes;          /* input bytes consumed */
+    uint64_t n_flush;        /* words the splitter emitted, empty ones included (main.cu:190-194) */
+    uint64_t n_empty;        /* of which empty */
+    uint64_t n_lost_empty;   /* empties before the first non-empty word (lost, main.cu:81,103) */
+    uint64_t stop;           /* offset at which input processing stopped (main.cu:185), == bytes if none */
+    uint64_t n_distinct;     /* distinct non-empty words counted */
+    uint64_t n_long_words;   /* words > 8 bytes (long-word path) */
+    uint64_t n_spilled;      /* short words that bypassed the shared-memory table */
+    uint64_t n_slow_tiles;   /* 512-byte tiles that needed the CR / NUL line-state path */
+    uint64_t table_grows;    /* times a device table was re-hashed into a larger one */
+    double device_ms;        /* sum of tokenizer-kernel times of this job (CUDA events), if measured */
+} wc_stats;
+
+WC_API void wc_config_default(wc_config *cfg);
+
+/* Replaces the allocation half of runMapReduce (main.cu:143-145,153-154). */
+WC_API int wc_create(wc_engine **out, const wc_config *cfg);
+WC_API void wc_destroy(wc_engine *e);
+
+/* Forget all counts; keeps the allocations.  Start of a new job. */
+WC_API int wc_reset(wc_engine *e);
+
+/* Feed the next `n` consecutive bytes of the input from HOST memory.  Replaces
+ * the fgets loop + cudaMemcpy H2D (main.cu:176-206, 147): bytes go through a
+ * pinned, double-buffered cudaMemcpyAsync pipeline overlapped with the
+ * tokenizer kernel.  `bytes` may be pageable or pinned; it is free on return. */
+WC_API int wc_feed(wc_engine *e, const void *bytes, size_t n);
+
+/* Count `n` bytes that are already in device memory (16-byte aligned, same
+ * device).  The piece must start at a line start of the input; every piece but
+ * the last must end with '\n'.  Asynchronous on the engine's stream; the
+ * buffer must stay valid until wc_sync()/wc_finish(). */
+WC_API int wc_count_device(wc_engine *e, const void *dev_bytes, size_t n, int last_piece);
+
+/* Wait for everything queued so far. */
+WC_API int wc_sync(wc_engine *e);
+
+/* End of input: drains the pipeline, applies the reduce semantics (mode) and
+ * returns the rows.  Replaces cudaReduce + the D2H copies (main.cu:155-158). */
+WC_API int wc_finish(wc_engine *e, wc_result **out);
+
+/* Rows are in the reference's output order (insertion order, main.cu:212). */
+WC_API size_t wc_result_rows(const wc_result *r);
+WC_API int wc_result_row(const wc_result *r, size_t i, const char **word, size_t *len, int64_t *count);
+WC_API uint64_t wc_result_row_first(const wc_result *r, size_t i); /* offset that flushed its first occurrence */
+WC_API int64_t wc_result_total(const wc_result *r);              /* "Total Count", main.cu:214,218 */
+WC_API int wc_result_stats(const wc_result *r, wc_stats *out);
+WC_API void wc_result_free(wc_result *r);
+
+/* Writes what main.cu prints after the echo (main.cu:210-218): separator, rows
+ * "word\tcount\n", separator, "Total Count:N\n".  Returns bytes needed. */
+WC_API size_t wc_result_render(const wc_result *r, char *buf, size_t cap);
+
+WC_API const char *wc_strerror(int status);
+WC_API const char *wc_last_error(const wc_engine *e);
+
+/* Pinned host memory for zero-staging wc_feed(). */
+WC_API int wc_host_alloc(void **p, size_t n);
+WC_API int wc_host_free(void *p);
+
+/* Time spent in tokenizer kernels since the last wc_reset(), measured with CUDA
+ * events on the engine's stream (call after wc_sync/wc_finish). */
+WC_API int wc_device_ms(wc_engine *e, double *ms, uint64_t *kernel_launches);
+
+/* The CUDA stream (cudaStream_t) the engine launches on, for callers that
+ * bracket work with their own events. */
+WC_API void *wc_stream(wc_engine *e);
+
+/* Test hook (no GPU needed): runs the host half of the reduce -- the order-free form of
+ * main.cu:57-108 -- on a caller-supplied table of exact counts.  `words` is the concatenation of
+ * the n distinct words. */
+WC_API int wc_debug_finalize(const char *words, const uint32_t *lens, const int64_t *counts,
+                             const uint64_t *firsts, size_t n, int mode, uint64_t n_empty,
+                             uint64_t n_lost_empty, wc_result **out);
+
+/* Test hooks (no GPU needed): the tokenizer's SWAR byte classification (delimiters of main.cu:188,
+ * line feeds, the 0x0D / 0x00 bytes that end a line's scan, main.cu:187,195) on 16 bytes, bit p of
+ * each mask = byte p; and the shared-memory table slot of a packed key. */
+WC_API int wc_debug_classify16(const uint8_t *bytes16, uint32_t *delim_mask, uint32_t *lf_mask,
+                               uint32_t *kill_mask);
+WC_API uint32_t wc_debug_smem_slot(uint64_t key);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

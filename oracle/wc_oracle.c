@@ -125,21 +125,30 @@ int orc_literal(const uint8_t *data, size_t n, int linecap, orc_result *out) {
 /* ------------------------------------------------------------------------- */
 
 typedef struct {
-    uint64_t off, first, hash;
+    uint64_t k0, k1; /* the word's first 16 bytes, zero padded (a word never contains 0x00) */
+    uint64_t off, first;
     int64_t count;
     uint32_t len, used;
 } fent;
 
 typedef struct {
     const uint8_t *data;
+    size_t n_data;
     fent *e;
     size_t cap, n; /* cap is a power of two */
     uint64_t n_flush, n_empty, n_lost_empty, p0;
     int seen_nonempty;
 } fmap;
 
-static inline uint64_t hash_bytes(const uint8_t *p, size_t len) {
-    uint64_t h = 0x9E3779B97F4A7C15ull ^ (len * 0xff51afd7ed558ccdull);
+static inline uint64_t mix_key(uint64_t k0, uint64_t k1, uint32_t len) {
+    uint64_t h = (k0 ^ (len * 0xff51afd7ed558ccdull)) * 0x9FB21C651E98DF25ull;
+    h ^= h >> 32;
+    h = (h ^ k1) * 0x9E3779B97F4A7C15ull;
+    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+    return h;
+}
+
+static inline uint64_t hash_tail(uint64_t h, const uint8_t *p, size_t len) {
     while (len >= 8) {
         uint64_t v; memcpy(&v, p, 8);
         h = (h ^ v) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
@@ -149,38 +158,54 @@ static inline uint64_t hash_bytes(const uint8_t *p, size_t len) {
         uint64_t v = 0; memcpy(&v, p, len);
         h = (h ^ v) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
     }
-    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
     return h;
 }
 
-static void fmap_init(fmap *m, const uint8_t *data, size_t cap) {
+static inline void load_key(const fmap *m, uint64_t off, uint32_t len, uint64_t *k0, uint64_t *k1) {
+    const uint8_t *p = m->data + off;
+    uint64_t a = 0, b = 0;
+    if (off + 16 <= m->n_data) {
+        memcpy(&a, p, 8); memcpy(&b, p + 8, 8);
+        if (len < 8) { a &= (1ull << (8 * len)) - 1; b = 0; }
+        else if (len < 16) b &= (1ull << (8 * (len - 8))) - 1; /* len == 8 -> mask 0 */
+    } else {
+        memcpy(&a, p, len < 8 ? len : 8);
+        if (len > 8) memcpy(&b, p + 8, (len < 16 ? len : 16) - 8);
+    }
+    *k0 = a; *k1 = b;
+}
+
+static void fmap_init(fmap *m, const uint8_t *data, size_t n_data, size_t cap) {
     memset(m, 0, sizeof(*m));
-    m->data = data; m->cap = cap;
+    m->data = data; m->n_data = n_data; m->cap = cap;
     m->e = (fent *)calloc(cap, sizeof(fent));
     m->p0 = UINT64_MAX;
 }
 
-static void fmap_add(fmap *m, uint64_t hash, uint64_t off, uint32_t len, int64_t count, uint64_t first);
+static void fmap_add(fmap *m, uint64_t k0, uint64_t k1, uint64_t off, uint32_t len, int64_t count, uint64_t first);
 
 static void fmap_grow(fmap *m) {
     fent *old = m->e; size_t ocap = m->cap;
     m->cap = ocap * 2; m->n = 0;
     m->e = (fent *)calloc(m->cap, sizeof(fent));
     for (size_t i = 0; i < ocap; i++)
-        if (old[i].used) fmap_add(m, old[i].hash, old[i].off, old[i].len, old[i].count, old[i].first);
+        if (old[i].used) fmap_add(m, old[i].k0, old[i].k1, old[i].off, old[i].len, old[i].count, old[i].first);
     free(old);
 }
 
-static void fmap_add(fmap *m, uint64_t hash, uint64_t off, uint32_t len, int64_t count, uint64_t first) {
+static void fmap_add(fmap *m, uint64_t k0, uint64_t k1, uint64_t off, uint32_t len, int64_t count, uint64_t first) {
+    uint64_t hash = mix_key(k0, k1, len);
+    if (len > 16) hash = hash_tail(hash, m->data + off + 16, len - 16);
     size_t mask = m->cap - 1, i = (size_t)hash & mask;
     for (;;) {
         fent *e = &m->e[i];
         if (!e->used) {
-            e->used = 1; e->hash = hash; e->off = off; e->len = len; e->count = count; e->first = first;
+            e->used = 1; e->k0 = k0; e->k1 = k1; e->off = off; e->len = len; e->count = count; e->first = first;
             if (++m->n * 10 > m->cap * 7) fmap_grow(m);
             return;
         }
-        if (e->hash == hash && e->len == len && memcmp(m->data + e->off, m->data + off, len) == 0) {
+        if (e->k0 == k0 && e->k1 == k1 && e->len == len &&
+            (len <= 16 || memcmp(m->data + e->off + 16, m->data + off + 16, len - 16) == 0)) {
             e->count += count;
             if (first < e->first) e->first = first;
             return;
@@ -198,7 +223,9 @@ static void fast_emit(void *vctx, uint64_t off, uint32_t len, uint64_t flush_off
         return;
     }
     if (!m->seen_nonempty) { m->seen_nonempty = 1; m->p0 = flush_off; }
-    fmap_add(m, hash_bytes(m->data + off, len), off, len, 1, flush_off);
+    uint64_t k0, k1;
+    load_key(m, off, len, &k0, &k1);
+    fmap_add(m, k0, k1, off, len, 1, flush_off);
 }
 
 static int cmp_lex(const void *a, const void *b, void *vdata) {
@@ -276,7 +303,7 @@ static void finalize(fmap *m, int mode, orc_result *out) {
 
 int orc_fast(const uint8_t *data, size_t n, int mode, orc_result *out) {
     memset(out, 0, sizeof(*out));
-    fmap m; fmap_init(&m, data, 1u << 16);
+    fmap m; fmap_init(&m, data, n, 1u << 16);
     split(data, n, 0, ORC_LINECAP_INF, fast_emit, &m, out);
     finalize(&m, mode, out);
     free(m.e);
@@ -286,14 +313,14 @@ int orc_fast(const uint8_t *data, size_t n, int mode, orc_result *out) {
 /* ---- multi-threaded variant: line-aligned slices, per-thread tables ------- */
 
 typedef struct {
-    const uint8_t *data; size_t lo, hi;
+    const uint8_t *data; size_t n, lo, hi;
     fmap m; orc_result st;
 } slice_job;
 
 static void *slice_main(void *arg) {
     slice_job *j = (slice_job *)arg;
     /* the table is keyed on absolute offsets into data */
-    fmap_init(&j->m, j->data, 1u << 16);
+    fmap_init(&j->m, j->data, j->n, 1u << 16);
     memset(&j->st, 0, sizeof(j->st));
     /* split() reports offsets relative to its own buffer start plus `base`;
      * passing the slice pointer with base = lo keeps them absolute. */
@@ -318,13 +345,13 @@ int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_resul
             hi = nl ? (size_t)(nl - data) + 1 : n;
         }
         if (hi == prev) continue;
-        jobs[nj].data = data; jobs[nj].lo = prev; jobs[nj].hi = hi;
+        jobs[nj].data = data; jobs[nj].n = n; jobs[nj].lo = prev; jobs[nj].hi = hi;
         prev = hi; nj++;
     }
     for (int t = 0; t < nj; t++) pthread_create(&th[t], NULL, slice_main, &jobs[t]);
     for (int t = 0; t < nj; t++) pthread_join(th[t], NULL);
 
-    fmap m; fmap_init(&m, data, 1u << 16);
+    fmap m; fmap_init(&m, data, n, 1u << 16);
     out->stop = n;
     for (int t = 0; t < nj; t++) {
         slice_job *j = &jobs[t];
@@ -336,7 +363,7 @@ int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_resul
         m.n_flush += j->m.n_flush; m.n_empty += j->m.n_empty;
         for (size_t i = 0; i < j->m.cap; i++)
             if (j->m.e[i].used)
-                fmap_add(&m, j->m.e[i].hash, j->m.e[i].off, j->m.e[i].len, j->m.e[i].count, j->m.e[i].first);
+                fmap_add(&m, j->m.e[i].k0, j->m.e[i].k1, j->m.e[i].off, j->m.e[i].len, j->m.e[i].count, j->m.e[i].first);
         out->n_chunks += j->st.n_chunks; out->n_cr += j->st.n_cr; out->n_nul += j->st.n_nul;
         if (j->st.max_line > out->max_line) out->max_line = j->st.max_line;
         if (j->st.stop < j->hi) { out->stop = j->st.stop; break; } /* main.cu:185: later slices never ran */
