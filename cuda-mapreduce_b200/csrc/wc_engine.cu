@@ -48,10 +48,12 @@ struct wc_engine {
     u64 launches = 0;
     u64 grows = 0;
 
-    // timing: one event pair per piece
+    // timing: per piece, events before the count kernel, after it, and after its roll-back companion
+    struct EvTriple { cudaEvent_t a, mid, b; };
     std::vector<cudaEvent_t> ev_pool;
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_used;
-    double device_ms = 0;
+    std::vector<EvTriple> ev_used;
+    double device_ms = 0;       // a -> b
+    double count_kernel_ms = 0; // a -> mid: the tokenizer/count kernel alone
 };
 
 #define CK(call)                                                                                         \
@@ -125,7 +127,7 @@ void wc_destroy(wc_engine *e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
     for (auto ev : e->ev_pool) cudaEventDestroy(ev);
-    for (auto &p : e->ev_used) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    for (auto &p : e->ev_used) { cudaEventDestroy(p.a); cudaEventDestroy(p.mid); cudaEventDestroy(p.b); }
     for (int i = 0; i < 2; i++) {
         if (e->d_chunk[i]) cudaFree(e->d_chunk[i]);
         if (e->ev_copied[i]) cudaEventDestroy(e->ev_copied[i]);
@@ -204,8 +206,8 @@ int wc_reset(wc_engine *e) {
     int rc = reset_device_state(e);
     if (rc != WC_OK) return rc;
     e->carry.clear();
-    e->consumed = 0; e->fed = 0; e->launches = 0; e->device_ms = 0;
-    for (auto &p : e->ev_used) { e->ev_pool.push_back(p.first); e->ev_pool.push_back(p.second); }
+    e->consumed = 0; e->fed = 0; e->launches = 0; e->device_ms = 0; e->count_kernel_ms = 0;
+    for (auto &p : e->ev_used) { e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.mid); e->ev_pool.push_back(p.b); }
     e->ev_used.clear();
     return WC_OK;
 }
@@ -224,18 +226,19 @@ static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_pie
     L.tiles_per_warp = (u32)tpw; L.last_piece = last_piece; L.negate = 0;
     L.ws = e->d_ws; L.n_ws = e->n_ws;
 
-    cudaEvent_t a, b;
-    for (cudaEvent_t *ev : {&a, &b}) {
+    cudaEvent_t a, mid, b;
+    for (cudaEvent_t *ev : {&a, &mid, &b}) {
         if (!e->ev_pool.empty()) { *ev = e->ev_pool.back(); e->ev_pool.pop_back(); }
         else CK(cudaEventCreate(ev));
     }
     CK(cudaEventRecord(a, e->stream));
     wc::count_kernel<<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+    CK(cudaEventRecord(mid, e->stream));
     L.negate = 1;
     wc::count_kernel<<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
     CK(cudaGetLastError());
     CK(cudaEventRecord(b, e->stream));
-    e->ev_used.emplace_back(a, b);
+    e->ev_used.push_back(wc_engine::EvTriple{a, mid, b});
     e->consumed += n;
     e->launches += 2;
     return WC_OK;
@@ -340,17 +343,20 @@ int wc_sync(wc_engine *e) {
     CK(cudaStreamSynchronize(e->stream));
     for (auto &p : e->ev_used) {
         float ms = 0;
-        CK(cudaEventElapsedTime(&ms, p.first, p.second));
+        CK(cudaEventElapsedTime(&ms, p.a, p.b));
         e->device_ms += ms;
-        e->ev_pool.push_back(p.first); e->ev_pool.push_back(p.second);
+        CK(cudaEventElapsedTime(&ms, p.a, p.mid));
+        e->count_kernel_ms += ms;
+        e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.mid); e->ev_pool.push_back(p.b);
     }
     e->ev_used.clear();
     return WC_OK;
 }
 
-int wc_device_ms(wc_engine *e, double *ms, uint64_t *kernel_launches) {
+int wc_device_ms(wc_engine *e, double *ms, double *count_kernel_ms, uint64_t *kernel_launches) {
     if (!e) return WC_ERR_INVALID;
     if (ms) *ms = e->device_ms;
+    if (count_kernel_ms) *count_kernel_ms = e->count_kernel_ms;
     if (kernel_launches) *kernel_launches = e->launches;
     return WC_OK;
 }
@@ -434,6 +440,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
     r->stats.n_slow_tiles = st.n_slow_tiles;
     r->stats.table_grows = e->grows;
     r->stats.device_ms = e->device_ms;
+    r->stats.count_kernel_ms = e->count_kernel_ms;
     wc::finalize_rows(std::move(blob), entries, e->cfg.mode, st.n_empty, lost, r);
     *out = r;
     return WC_OK;

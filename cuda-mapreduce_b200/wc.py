@@ -42,6 +42,7 @@ class Stats(C.Structure):
         ("bytes", C.c_uint64), ("n_flush", C.c_uint64), ("n_empty", C.c_uint64), ("n_lost_empty", C.c_uint64),
         ("stop", C.c_uint64), ("n_distinct", C.c_uint64), ("n_long_words", C.c_uint64), ("n_spilled", C.c_uint64),
         ("n_slow_tiles", C.c_uint64), ("table_grows", C.c_uint64), ("device_ms", C.c_double),
+        ("count_kernel_ms", C.c_double),
     ]
 
 
@@ -92,7 +93,7 @@ def lib():
     L.wc_last_error.restype = C.c_char_p
     L.wc_host_alloc.argtypes = [C.POINTER(vp), sz]
     L.wc_host_free.argtypes = [vp]
-    L.wc_device_ms.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u64)]
+    L.wc_device_ms.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(u64)]
     L.wc_stream.argtypes = [vp]
     L.wc_stream.restype = vp
     L.wc_debug_finalize.argtypes = [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(i64), C.POINTER(u64), sz, C.c_int,
@@ -197,9 +198,9 @@ class Engine:
         return Result(r, keep_rows)
 
     def device_ms(self):
-        ms, n = C.c_double(), C.c_uint64()
-        self._ck(lib().wc_device_ms(self.h, C.byref(ms), C.byref(n)))
-        return ms.value, n.value
+        ms, kms, n = C.c_double(), C.c_double(), C.c_uint64()
+        self._ck(lib().wc_device_ms(self.h, C.byref(ms), C.byref(kms), C.byref(n)))
+        return ms.value, kms.value, n.value
 
     def stream(self):
         return lib().wc_stream(self.h)

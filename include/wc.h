@@ -83,7 +83,8 @@ typedef struct wc_stats {
     uint64_t n_spilled;      /* short words that bypassed the shared-memory table */
     uint64_t n_slow_tiles;   /* 512-byte tiles that needed the CR / NUL line-state path */
     uint64_t table_grows;    /* times a device table was re-hashed into a larger one */
-    double device_ms;        /* sum of tokenizer-kernel times of this job (CUDA events), if measured */
+    double device_ms;        /* device time of this job's kernels (CUDA events on the engine's stream) */
+    double count_kernel_ms;  /* of which the tokenizer/count kernel alone */
 } wc_stats;
 
 WC_API void wc_config_default(wc_config *cfg);
@@ -133,9 +134,10 @@ WC_API const char *wc_last_error(const wc_engine *e);
 WC_API int wc_host_alloc(void **p, size_t n);
 WC_API int wc_host_free(void *p);
 
-/* Time spent in tokenizer kernels since the last wc_reset(), measured with CUDA
- * events on the engine's stream (call after wc_sync/wc_finish). */
-WC_API int wc_device_ms(wc_engine *e, double *ms, uint64_t *kernel_launches);
+/* Device time since the last wc_reset(), measured with CUDA events on the engine's stream (call
+ * after wc_sync/wc_finish): all kernels of the job, the tokenizer/count kernel alone, and how many
+ * kernels were launched. */
+WC_API int wc_device_ms(wc_engine *e, double *ms, double *count_kernel_ms, uint64_t *kernel_launches);
 
 /* The CUDA stream (cudaStream_t) the engine launches on, for callers that
  * bracket work with their own events. */

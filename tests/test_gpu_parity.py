@@ -1,0 +1,296 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libwc.so), against the oracle and
+against the golden stdout of the reference's own code.  Bit-exact: rows, order, counts, totals and
+the splitter's counters.  Run on the B200 box with `pytest -m gpu`."""
+import os
+import random
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, load_pkg
+from oracle import orc as O
+from test_oracle import ALPHABET, DELIMS, random_text
+
+pytestmark = pytest.mark.gpu
+
+SMALL = dict(short_table_log2=14, long_table_log2=14, arena_bytes=8 << 20)
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    return load_pkg()
+
+
+@pytest.fixture(scope="module")
+def eng_ref(pkg):
+    e = pkg.Engine(mode=pkg.MODE_REF, chunk_bytes=1 << 20, **SMALL)
+    yield e
+    e.close()
+
+
+@pytest.fixture(scope="module")
+def eng_exact(pkg):
+    e = pkg.Engine(mode=pkg.MODE_EXACT, chunk_bytes=1 << 20, **SMALL)
+    yield e
+    e.close()
+
+
+def check_against_oracle(engine, data, mode=O.MODE_REF, feed=None, what=""):
+    engine.reset()
+    if feed is None:
+        engine.feed(data)
+    else:
+        feed(engine, data)
+    got = engine.finish()
+    exp = O.fast(data, mode)
+    assert got.stats["n_flush"] == exp.n_flush, what
+    assert got.stats["n_empty"] == exp.n_empty, what
+    assert got.stats["stop"] == exp.stop, what
+    assert got.pairs() == exp.pairs(), what
+    assert got.total == exp.total, what
+    assert got.firsts == [f for _, _, f in exp.rows], what
+    if mode == O.MODE_REF:
+        assert got.stats["n_lost_empty"] == exp.n_lost_empty, what
+    return got
+
+
+def test_golden_vectors(eng_ref, golden):
+    for name, data, expect in golden:
+        if data is None:
+            continue
+        got = check_against_oracle(eng_ref, data, what=name)
+        if O.fast(data).max_line <= 99:  # literal reference semantics == lifted semantics (A.2 L5)
+            assert expect.endswith(got.rendered), name
+
+
+def test_golden_vectors_exact_mode(eng_exact, golden):
+    for name, data, _ in golden:
+        if data is not None:
+            check_against_oracle(eng_exact, data, O.MODE_EXACT, what=name)
+
+
+def test_cli_stdout_is_byte_identical_to_reference(pkg, golden):
+    exe = os.path.join(ROOT, "cuda-mapreduce_b200", "wordcount")
+    assert os.path.exists(exe)
+    picked = [g for g in golden if g[1] is None or O.fast(g[1]).max_line <= 99]
+    picked = picked[:30] + picked[-10:]
+    with tempfile.TemporaryDirectory() as td:
+        for name, data, expect in picked:
+            p = os.path.join(td, "test.txt")
+            if data is None:
+                if os.path.exists(p):
+                    os.remove(p)
+            else:
+                with open(p, "wb") as f:
+                    f.write(data)
+            r = subprocess.run([exe], cwd=td, capture_output=True, timeout=120)
+            assert r.returncode == 0, (name, r.stderr)
+            assert r.stdout == expect, name
+
+
+@pytest.mark.skipif(not os.path.exists(O.REF_GPU), reason="oracle/_ref/main_sm100a not built")
+def test_real_reference_binary_on_this_gpu(golden):
+    """L0: the reference's unmodified main.cu, compiled by nvcc for sm_100a, run on this GPU."""
+    by = {n: (d, e) for n, d, e in golden}
+    with tempfile.TemporaryDirectory() as td:
+        for name in ("test_txt", "c2_01_prefix", "c2_02_prefix_order", "c2_03_empty_to_row0", "c2_07_crlf"):
+            data, expect = by[name]
+            with open(os.path.join(td, "test.txt"), "wb") as f:
+                f.write(data)
+            r = subprocess.run([O.REF_GPU], cwd=td, capture_output=True, timeout=120)
+            assert r.stdout == expect, name
+
+
+def test_fuzz_small(eng_ref, eng_exact):
+    rng = random.Random(2024)
+    for i in range(250):
+        data = random_text(rng, rng.randint(0, 300), weird=rng.choice([0.0, 0.05, 0.3]))
+        check_against_oracle(eng_ref, data, what=data)
+        if i % 5 == 0:
+            check_against_oracle(eng_exact, data, O.MODE_EXACT, what=data)
+
+
+def test_fuzz_arbitrary_bytes(eng_ref):
+    rng = np.random.default_rng(99)
+    pool = np.frombuffer(b"ab \n\r\0\tz,\xc3\xa9 \n  a", dtype=np.uint8)
+    for i in range(120):
+        n = int(rng.integers(0, 5000))
+        data = pool[rng.integers(0, len(pool), size=n)].tobytes()
+        check_against_oracle(eng_ref, data, what=i)
+
+
+def long_text(rng, n_tokens, weird):
+    return random_text(rng, n_tokens, weird)
+
+
+def test_tile_and_chunk_boundaries(pkg):
+    """Sizes around the 512-byte warp tile, the 8 KiB CTA step and a tiny streaming chunk; words and
+    delimiter runs placed to straddle them."""
+    rng = random.Random(77)
+    with pkg.Engine(chunk_bytes=4096, **SMALL) as e:
+        for n in [1, 2, 15, 16, 17, 511, 512, 513, 1023, 1024, 1025, 4095, 4096, 4097, 8191, 8192, 8193,
+                  12288, 65536 + 3]:
+            body = bytearray()
+            while len(body) < n:
+                w = rng.choice(ALPHABET + [b"x" * rng.randint(1, 40)])
+                body += w + rng.choice([b" ", b" ", b"\n", b"  "])
+            data = bytes(body[:n])
+            check_against_oracle(e, data, what=n)
+        # a delimiter exactly at every tile edge, then a word ending exactly at every tile edge
+        for shift in range(0, 20):
+            data = (b"a" * (511 - shift) + b" " + b"bcd ef\n" * 80)[: 512 * 3 + shift] + b"\n"
+            check_against_oracle(e, data, what=("edge", shift))
+
+
+def test_feed_in_ragged_calls(pkg):
+    rng = random.Random(5)
+    data = random_text(rng, 60000, weird=0.01)
+    data = data.replace(b"\n\n", b"\n").replace(b"\0", b"")
+
+    def ragged(engine, d):
+        pos = 0
+        while pos < len(d):
+            k = rng.choice([1, 2, 7, 100, 3000, 5000, 70000])
+            engine.feed(d[pos:pos + k])
+            pos += k
+
+    with pkg.Engine(chunk_bytes=8192, **SMALL) as e:
+        for _ in range(3):
+            check_against_oracle(e, data, feed=ragged)
+
+
+def test_line_longer_than_chunk(pkg):
+    rng = random.Random(6)
+    line = b" ".join(rng.choice(ALPHABET) for _ in range(20000))  # ~100 KB without a newline
+    data = b"head words here\n" + line + b"\nlast line\n" + line  # the last one is never terminated
+    with pkg.Engine(chunk_bytes=4096, **SMALL) as e:
+        check_against_oracle(e, data)
+
+
+def test_stop_rules_across_chunks(pkg):
+    rng = random.Random(8)
+    base = random_text(rng, 30000, weird=0.0).replace(b"\n\n", b"\n")
+    assert O.fast(base).stop == len(base)
+    with pkg.Engine(chunk_bytes=4096, **SMALL) as e:
+        for cut in (0, 1, 5000, len(base) // 2):
+            lines = base.split(b"\n")
+            k = max(1, len(lines) * cut // max(len(base), 1))
+            data = b"\n".join(lines[:k]) + b"\n\n" + b"\n".join(lines[k:]) + b"\n"
+            exp = O.fast(data)
+            assert exp.stop < len(data)
+            check_against_oracle(e, data, what=("blank", cut))
+        check_against_oracle(e, b"\n" + base, what="blank first")
+        check_against_oracle(e, base.rstrip(b"\n") + b"\nq", what="1-byte tail")
+        check_against_oracle(e, base.rstrip(b"\n") + b"\n ", what="1-byte space tail")
+        check_against_oracle(e, base + b"ab\0cd ef\n" + base[:500], what="nul mid line")
+        check_against_oracle(e, base + b"a\0cd ef\n" + base[:500], what="nul at offset 1: stop")
+        check_against_oracle(e, base + b"\0cd ef\n" + base[:500], what="nul at offset 0: stop")
+
+
+def test_crlf_and_nul_text(pkg):
+    rng = random.Random(9)
+    unix = random_text(rng, 80000, weird=0.0).replace(b"\n\n", b"\n")
+    dos = unix.replace(b"\n", b"\r\n")
+    with pkg.Engine(chunk_bytes=1 << 16, **SMALL) as e:
+        got = check_against_oracle(e, dos, what="crlf")
+        assert got.stats["n_slow_tiles"] > 0
+        stray = bytearray(unix)
+        for _ in range(200):
+            stray[rng.randrange(len(stray))] = rng.choice([0x0D, 0x00])
+        check_against_oracle(e, bytes(stray), what="stray cr/nul")
+
+
+def test_device_resident_input(pkg):
+    import torch
+    rng = random.Random(10)
+    data = random_text(rng, 200000, weird=0.0).replace(b"\n\n", b"\n")
+    dev = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+    with pkg.Engine(**SMALL) as e:
+        for _ in range(2):  # twice: reset leaves no residue
+            e.reset()
+            e.count_device(dev.data_ptr(), dev.numel(), last_piece=True)
+            got = e.finish()
+            exp = O.fast(data)
+            assert got.pairs() == exp.pairs() and got.total == exp.total
+            assert (got.stats["n_flush"], got.stats["n_empty"], got.stats["stop"]) == (exp.n_flush, exp.n_empty, exp.stop)
+        # two pieces, cut at a line start
+        cut = data.index(b"\n", len(data) // 2) + 1
+        e.reset()
+        e.count_device(dev.data_ptr(), cut, last_piece=False)
+        tail = dev[cut:].clone()  # 16-byte aligned copy
+        e.count_device(tail.data_ptr(), tail.numel(), last_piece=True)
+        got = e.finish()
+        assert got.pairs() == exp.pairs() and got.total == exp.total
+
+
+def test_compat_runMapReduce(pkg, golden):
+    """The reference's own entry point (main.cu:133) with its struct layouts, served by libwc.so."""
+    lines = [[b"Hello", b"World", b"EveryOne"], [b"World", b"Good", b"News"], [b"Good", b"Morning", b"Hello"]]
+    rows = pkg.run_map_reduce(lines)
+    assert rows == [(b"Hello", 2), (b"World", 2), (b"EveryOne", 1), (b"Good", 2), (b"News", 1), (b"Morning", 1)]
+    # prefix rule and empty words, as the reference's reducer treats them (App. C.2 #1-#3)
+    assert pkg.run_map_reduce([[b"Hello", b"He", b"He"]]) == [(b"Hello", 3)]
+    assert pkg.run_map_reduce([[b"He", b"Hello", b"He"]]) == [(b"He", 2), (b"Hello", 1)]
+    assert pkg.run_map_reduce([[b"a", b"", b"b", b"a"]]) == [(b"a", 3), (b"b", 1)]
+    assert pkg.run_map_reduce([[b"", b"", b"a", b"b"]]) == [(b"a", 1), (b"b", 1)]
+    assert pkg.run_map_reduce([]) == []
+
+
+def corpus_check(pkg, config, nbytes, engine_kw, straddle=(), feed_chunks=None):
+    from tools.corpus import Corpus
+    c = Corpus(config, total_bytes=nbytes, straddle=straddle)
+    data = c.bytes()
+    exp = O.fast_mt(data)
+    with pkg.Engine(**engine_kw) as e:
+        e.feed(data)
+        got = e.finish()
+    assert got.stats["n_flush"] == exp.n_flush and got.stats["n_empty"] == exp.n_empty
+    assert got.stats["stop"] == exp.stop == data.size
+    assert got.total == exp.total
+    assert got.pairs() == exp.pairs()
+    return got, exp, data
+
+
+def test_config2_sample_zipf_50k(pkg):
+    got, exp, data = corpus_check(pkg, 2, 48 * (1 << 20), dict(chunk_bytes=16 << 20, short_table_log2=18, long_table_log2=16))
+    assert got.stats["n_slow_tiles"] == 0 and exp.max_line <= 99  # generator invariants G2/G3
+    assert got.stats["n_distinct"] > 40000
+
+
+def test_config3_sample_zipf_1m(pkg):
+    got, exp, _ = corpus_check(pkg, 3, 64 * (1 << 20), dict(chunk_bytes=32 << 20, short_table_log2=21, long_table_log2=21))
+    assert got.stats["n_distinct"] > 300000
+
+
+def test_config5_sample_adversarial(pkg):
+    n = 12_000_000
+    got, exp, _ = corpus_check(pkg, 5, n, dict(chunk_bytes=4 << 20, short_table_log2=16, long_table_log2=22,
+                                               arena_bytes=128 << 20), straddle=(4 << 20, 6_000_000))
+    assert exp.max_line > 99 and got.stats["n_long_words"] > 500000
+
+
+def test_config2_full_size_1GB(pkg):
+    """BASELINE.json config 2 at full size: 10^9 bytes, V = 50k, Zipf 1.1 -- bit-exact against the
+    multi-threaded oracle, plus size-independent properties."""
+    import torch
+    from tools.corpus import Corpus
+    c = Corpus(2)
+    host = torch.empty(c.total, dtype=torch.uint8).pin_memory()
+    c.fill(host.numpy())
+    dev = host.cuda()
+    with pkg.Engine(short_table_log2=18, long_table_log2=16) as e:
+        e.count_device(dev.data_ptr(), dev.numel(), last_piece=True)
+        got = e.finish()
+        assert got.stats["n_empty"] == 0 and got.stats["stop"] == c.total and got.stats["n_slow_tiles"] == 0
+        assert got.total == got.stats["n_flush"]                      # every word lands in exactly one row
+        assert got.stats["n_flush"] == int((dev == 32).sum() + (dev == 10).sum())  # one word per delimiter
+        assert got.firsts == sorted(got.firsts)
+        # streaming the same bytes from host memory gives the same rows
+        e.reset()
+        e.feed((host.data_ptr(), host.numel()))
+        got2 = e.finish()
+        assert got2.pairs() == got.pairs() and got2.total == got.total
+    exp = O.fast_mt(host.numpy())
+    assert got.pairs() == exp.pairs() and got.total == exp.total and got.stats["n_flush"] == exp.n_flush
