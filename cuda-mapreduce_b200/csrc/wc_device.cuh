@@ -322,9 +322,10 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
             __syncthreads();
             if (tid == 0 && first != 0xFFFFFFFFu) { st->p0 = L.ws[first].p0; st->p0_found = 1; }
         }
+        // Nothing to undo unless STOP lies inside this piece (a piece after STOP was never counted).
         const u64 stop = stop_seen;
-        if (stop == kNone || stop >= L.base + L.n) return;
-        range_lo = stop > L.base ? stop - L.base : 0;
+        if (stop == kNone || stop >= L.base + L.n || stop < L.base) return;
+        range_lo = stop - L.base;
     } else {
         const u64 stop = stop_seen;
         if (stop != kNone && stop < L.base) { // the reference stopped reading before this piece
