@@ -159,6 +159,7 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="config2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
@@ -249,13 +250,15 @@ def main():
         eng.feed((host.data_ptr(), nbytes))
         return eng.finish(keep_rows=False)
 
-    step_e2e()
+    e2e_steps = 0 if args.no_e2e else max(3, args.steps // 2)
+    if e2e_steps:
+        step_e2e()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(max(3, args.steps // 2)):
-        r2 = step_e2e()
+    for _ in range(e2e_steps):
+        step_e2e()
     torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - t0) / max(3, args.steps // 2)
+    e2e_s = (time.perf_counter() - t0) / max(1, e2e_steps)
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)

@@ -266,7 +266,7 @@ def test_config3_sample_zipf_1m(pkg):
 
 def test_config5_sample_adversarial(pkg):
     n = 12_000_000
-    got, exp, _ = corpus_check(pkg, 5, n, dict(chunk_bytes=4 << 20, short_table_log2=16, long_table_log2=22,
+    got, exp, _ = corpus_check(pkg, 5, n, dict(chunk_bytes=4 << 20, short_table_log2=21, long_table_log2=22,
                                                arena_bytes=128 << 20), straddle=(4 << 20, 6_000_000))
     assert exp.max_line > 99 and got.stats["n_long_words"] > 500000
 
