@@ -465,3 +465,138 @@ extern "C" int wc_debug_classify16(const uint8_t *bytes16, uint32_t *delim_mask,
 extern "C" uint32_t wc_debug_smem_slot(uint64_t key) {
     return (uint32_t)(((uint64_t)wc::hash32((u32)key, (u32)(key >> 32)) * wc::kSmemEntries) >> 32);
 }
+
+// ------------------------------------------------------------------------------------------------
+// wc_count_device_static: the count kernel for callers that must not allocate.
+//
+// The regular engine keeps the kernel's working state -- the Status block and one WarpSummary per
+// warp -- in memory it cudaMallocs in wc_create().  Some users of this library cannot do that: a
+// host application that has handed the whole device heap to its own pool allocator (a cudaMalloc
+// there fails or steals from the pool), or code on a latency-critical path, where cudaMalloc and
+// cudaFree stall the whole device while they run.  For them the same kernel is offered with its
+// working state in a fixed array that is part of the library image; the caller supplies the text
+// and every buffer the results are written to.
+//
+// g_static_scratch lives in every GPU's memory from the moment the library is loaded there until
+// the process exits (kStaticScratchBytes, about 97 KiB).  In host code the name `g_static_scratch`
+// is only a handle for the symbol, not a device address, so the address the kernel needs is looked
+// up once per device with cudaGetSymbolAddress() while that device is current.
+namespace {
+
+constexpr u32 kStaticMaxWarps = 4096; // 256 SMs x 16 warps: more than any sm_100 part has
+constexpr size_t kStaticStatusBytes = 256;
+constexpr size_t kStaticScratchBytes = kStaticStatusBytes + sizeof(wc::WarpSummary) * kStaticMaxWarps;
+static_assert(sizeof(wc::Status) <= kStaticStatusBytes, "Status must fit its slot");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticMaxDevices = 64;
+struct StaticDevice {
+    bool ready;
+    unsigned char *scratch; // device address of g_static_scratch on this device
+    int num_sms;
+};
+StaticDevice g_static_dev[kStaticMaxDevices];
+thread_local char g_static_err[192];
+
+// Start-of-call state: everything zero except the "none yet" markers; arena unit 0 is never used.
+__global__ void static_begin_kernel(wc::Status *st) {
+    if (threadIdx.x == 0) {
+        wc::Status s;
+        memset(&s, 0, sizeof(s));
+        s.stop = wc::kNone; s.p0 = wc::kNone; s.arena_used = 1;
+        *st = s;
+    }
+}
+
+__global__ void static_end_kernel(const wc::Status *st, u64 *out) {
+    if (threadIdx.x == 0) {
+        out[0] = st->n_flush; out[1] = st->n_empty; out[2] = st->stop; out[3] = st->p0;
+        out[4] = st->lost_empty; out[5] = st->p0_found; out[6] = st->err; out[7] = st->s_entries;
+        out[8] = st->l_entries; out[9] = st->arena_used; out[10] = st->n_long; out[11] = st->n_spill;
+    }
+}
+
+int static_fail(int code, const char *what, cudaError_t ce) {
+    if (ce != cudaSuccess) snprintf(g_static_err, sizeof(g_static_err), "%s: %s", what, cudaGetErrorString(ce));
+    else snprintf(g_static_err, sizeof(g_static_err), "%s", what);
+    return code;
+}
+
+} // namespace
+
+extern "C" const char *wc_static_last_error(void) { return g_static_err; }
+
+extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n, uint64_t *dev_short_table,
+                                      uint32_t short_log2, uint64_t *dev_long_table, uint32_t long_log2,
+                                      uint64_t *dev_arena, uint64_t arena_bytes, uint64_t *dev_counters,
+                                      void *stream_handle) {
+    g_static_err[0] = 0;
+    if (device < 0 || device >= kStaticMaxDevices || (!dev_text && n) || !dev_short_table || !dev_long_table ||
+        !dev_arena || !dev_counters || short_log2 < 10 || short_log2 > 34 || long_log2 < 10 || long_log2 > 34 ||
+        arena_bytes < 4096)
+        return static_fail(WC_ERR_INVALID, "wc_count_device_static: bad argument", cudaSuccess);
+    if (((uintptr_t)dev_text & 15) != 0)
+        return static_fail(WC_ERR_UNALIGNED, "wc_count_device_static: text must be 16-byte aligned", cudaSuccess);
+    if (n > (size_t)WC_STATIC_MAX_BYTES)
+        return static_fail(WC_ERR_TOO_LARGE, "wc_count_device_static: text larger than WC_STATIC_MAX_BYTES", cudaSuccess);
+
+    int prev_device = 0;
+    cudaError_t ce = cudaGetDevice(&prev_device);
+    if (ce != cudaSuccess) return static_fail(WC_ERR_CUDA, "cudaGetDevice", ce);
+    if ((ce = cudaSetDevice(device)) != cudaSuccess) return static_fail(WC_ERR_CUDA, "cudaSetDevice", ce);
+    int rc = WC_OK;
+    do {
+        StaticDevice &sd = g_static_dev[device];
+        if (!sd.ready) { // first call on this device: find the array's address here, raise the kernel's smem limit
+            void *addr = nullptr;
+            if ((ce = cudaGetSymbolAddress(&addr, g_static_scratch)) != cudaSuccess) {
+                rc = static_fail(WC_ERR_CUDA, "cudaGetSymbolAddress(g_static_scratch)", ce); break;
+            }
+            int sms = 0;
+            if ((ce = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) {
+                rc = static_fail(WC_ERR_CUDA, "cudaDeviceGetAttribute", ce); break;
+            }
+            if ((ce = cudaFuncSetAttribute(wc::count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)wc::kSmemTotal)) != cudaSuccess) {
+                rc = static_fail(WC_ERR_CUDA, "cudaFuncSetAttribute", ce); break;
+            }
+            sd.scratch = (unsigned char *)addr; sd.num_sms = sms; sd.ready = true;
+        }
+        const u32 n_ws = (u32)sd.num_sms * wc::kWarps;
+        if (n_ws > kStaticMaxWarps) {
+            rc = static_fail(WC_ERR_TOO_LARGE, "wc_count_device_static: this GPU has more SMs than the static scratch covers", cudaSuccess);
+            break;
+        }
+        cudaStream_t stream = (cudaStream_t)stream_handle;
+        wc::Status *st = (wc::Status *)sd.scratch;
+        wc::WarpSummary *ws = (wc::WarpSummary *)(sd.scratch + kStaticStatusBytes);
+        const size_t s_n = (size_t)1 << short_log2, l_n = (size_t)1 << long_log2;
+        wc::Tables T;
+        T.s_keys = (u64 *)dev_short_table; T.s_counts = T.s_keys + s_n; T.s_finv = T.s_keys + 2 * s_n; T.s_log2 = short_log2;
+        T.l_refs = (u64 *)dev_long_table; T.l_counts = T.l_refs + l_n; T.l_finv = T.l_refs + 2 * l_n; T.l_log2 = long_log2;
+        T.arena = (u64 *)dev_arena; T.arena_units = arena_bytes / 8; T.st = st;
+
+        // results start from zero; the shared working state is re-initialised on every call
+        if ((ce = cudaMemsetAsync(dev_short_table, 0, 3 * s_n * sizeof(u64), stream)) != cudaSuccess ||
+            (ce = cudaMemsetAsync(dev_long_table, 0, 3 * l_n * sizeof(u64), stream)) != cudaSuccess) {
+            rc = static_fail(WC_ERR_CUDA, "cudaMemsetAsync", ce); break;
+        }
+        static_begin_kernel<<<1, 32, 0, stream>>>(st);
+        if (n > 0) {
+            const u64 tiles = (n + wc::kTile - 1) / wc::kTile;
+            const u64 warps = (u64)sd.num_sms * wc::kWarps;
+            const u64 tpw = (tiles + warps - 1) / warps;
+            wc::Launch L;
+            L.buf = (const uint8_t *)dev_text; L.n = n; L.base = 0; L.tiles_per_warp = (u32)tpw;
+            L.last_piece = 1; L.negate = 0; L.ws = ws; L.n_ws = n_ws;
+            wc::count_kernel<<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
+            L.negate = 1;
+            wc::count_kernel<<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
+        }
+        static_end_kernel<<<1, 32, 0, stream>>>(st, (u64 *)dev_counters);
+        if ((ce = cudaGetLastError()) != cudaSuccess) { rc = static_fail(WC_ERR_CUDA, "kernel launch", ce); break; }
+    } while (0);
+    cudaSetDevice(prev_device);
+    return rc;
+}

@@ -101,6 +101,8 @@ def lib():
     L.wc_debug_classify16.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.wc_debug_smem_slot.argtypes = [u64]
     L.wc_debug_smem_slot.restype = C.c_uint32
+    L.wc_count_device_static.argtypes = [C.c_int, vp, sz, vp, C.c_uint32, vp, C.c_uint32, vp, u64, vp, vp]
+    L.wc_static_last_error.restype = C.c_char_p
     L.runMapReduce.argtypes = [vp, C.c_int, vp, C.POINTER(C.c_int)]
     L.runMapReduce.restype = None
     _lib = L

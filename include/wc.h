@@ -143,6 +143,48 @@ WC_API int wc_device_ms(wc_engine *e, double *ms, double *count_kernel_ms, uint6
  * bracket work with their own events. */
 WC_API void *wc_stream(wc_engine *e);
 
+/* ---- wc_count_device_static: counting without any allocation -------------------------------
+ *
+ * No counterpart in the reference (whose runMapReduce cudaMallocs and cudaFrees on every call,
+ * main.cu:143-161).  It exists for callers that cannot allocate device memory at all: programs
+ * that gave the whole device heap to their own pool, and hot paths where the device-wide stall of
+ * cudaMalloc/cudaFree is not acceptable.  It runs the same tokenizer/count kernel as
+ * wc_count_device(), but the kernel's working state sits in a fixed array inside the library image
+ * (about 97 KiB, resident on every GPU that loads libwc.so until the process exits) and the caller
+ * provides the text and every result buffer.  The call makes no cudaMalloc/cudaFree and no other
+ * allocating call, on the device or on the host.
+ *
+ *   dev_text          n bytes of text in device memory, 16-byte aligned; the WHOLE input (it is
+ *                     treated as starting at a line start and ending the input).
+ *   dev_short_table   3 << short_log2 uint64: keys | counts | ~first-offset of words of 1..8 bytes
+ *                     (a key is the word itself, little-endian, zero padded).
+ *   dev_long_table    3 << long_log2 uint64: refs | counts | ~first-offset of longer words; a ref is
+ *                     (24-bit tag << 40) | unit index into dev_arena.
+ *   dev_arena         arena_bytes of storage for the longer words: unit[i] = length in bytes,
+ *                     unit[i+1...] = the bytes, zero padded to 8.
+ *   dev_counters      WC_STATIC_COUNTERS uint64 written at the end: n_flush, n_empty, stop (~0 if
+ *                     none), p0 (~0 if none), lost_empty, p0_found, err (0 = ok, else a table or the
+ *                     arena was too small), short slots used, long slots used, arena units used,
+ *                     long words, spilled words.
+ *   stream            a cudaStream_t (NULL = the default stream); everything is asynchronous on it.
+ *
+ * The tables are cleared by the call itself, so the results describe this text alone.  Limits:
+ * n <= WC_STATIC_MAX_BYTES and a GPU of at most 256 SMs; anything larger is refused with
+ * WC_ERR_TOO_LARGE before any work is queued (wc_static_last_error() says which).
+ *
+ * The first call on each device looks up the array's device address and raises the kernel's
+ * shared-memory limit; make that first call before starting any stream capture.  All calls on a
+ * device share the one array and it keeps whatever the previous call left, so the call resets it
+ * first -- which also means two calls whose GPU work overlaps (different streams, different
+ * threads) corrupt each other: run them one after the other. */
+#define WC_STATIC_MAX_BYTES (1ull << 36)
+#define WC_STATIC_COUNTERS 12
+WC_API int wc_count_device_static(int device, const void *dev_text, size_t n, uint64_t *dev_short_table,
+                                  uint32_t short_log2, uint64_t *dev_long_table, uint32_t long_log2,
+                                  uint64_t *dev_arena, uint64_t arena_bytes, uint64_t *dev_counters,
+                                  void *stream);
+WC_API const char *wc_static_last_error(void);
+
 /* Test hook (no GPU needed): runs the host half of the reduce -- the order-free form of
  * main.cu:57-108 -- on a caller-supplied table of exact counts.  `words` is the concatenation of
  * the n distinct words. */
