@@ -18,21 +18,22 @@ namespace wc {
 typedef unsigned long long u64;
 typedef unsigned int u32;
 
-constexpr int kTile = 512;                 // bytes per warp-tile: 32 lanes x 16 B
+constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 B
+constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = 16;                 // warps per CTA
 constexpr int kThreads = kWarps * 32;
-constexpr u32 kSmemEntries = 11264;        // 16-byte entries of the per-CTA table (176 KiB)
-constexpr u32 kSmemLimit = 9011;           // stop claiming new slots at 80 % load
-constexpr int kSmemMaxProbe = 12;
-constexpr int kRingBytes = 1024;           // per warp: previous + current tile
-constexpr int kLongQueue = 64;             // per warp: pending long words
+constexpr u32 kSmemEntries = 10880;        // 16-byte entries of the per-CTA table (170 KiB)
+constexpr int kRingBytes = 1072;           // per warp: 16 B tail of the previous tile + the tile + slack
+constexpr int kDlCap = 512;                // per warp: delimiter list entries
+constexpr int kDlBytes = kDlCap * 2;
+constexpr int kQueue = 64;                 // per warp: pending spilled words / pending long words
 constexpr u64 kNone = ~0ull;
 
+constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + 2 * kQueue * 12;
 constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16;
-constexpr size_t kSmemRingBytes = (size_t)kWarps * kRingBytes;
-constexpr size_t kSmemDlistBytes = (size_t)kWarps * kTile * 2;
-constexpr size_t kSmemQueueBytes = (size_t)kWarps * kLongQueue * 12;
-constexpr size_t kSmemTotal = kSmemTableBytes + kSmemRingBytes + kSmemDlistBytes + kSmemQueueBytes;
+constexpr size_t kSmemTotal = kSmemTableBytes + (size_t)kWarps * kWarpSmemBytes;
+static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
+static_assert(kSmemTotal <= 232448 - 64, "more shared memory than an sm_100 CTA can have");
 
 enum : u32 { kErrShortFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u };
 
@@ -156,25 +157,24 @@ __device__ __forceinline__ u64 warp_sum64(u64 v) {
 
 // ------------------------------------------------------- global short table
 
-struct ThreadCounters { u32 s_new, l_new, n_long, n_spill; };
-
-__device__ __forceinline__ void gs_insert(const Tables &T, u64 key, u64 delta, u64 first_abs,
-                                          ThreadCounters &tc) {
+// Adds `delta` occurrences of a 1..8-byte word to the global table; returns 1 if it claimed a new slot.
+__device__ __forceinline__ u32 gs_insert(const Tables &T, u64 key, u64 delta, u64 first_abs) {
     const u64 mask = (1ull << T.s_log2) - 1;
     u64 slot = mix64(key) >> (64 - T.s_log2);
+    u32 is_new = 0;
     for (u32 probes = 0;; ++probes) {
         u64 k = __ldcg(&T.s_keys[slot]);
         if (k == 0) {
             k = atomicCAS(&T.s_keys[slot], 0ull, key);
-            if (k == 0) { tc.s_new++; k = key; }
+            if (k == 0) { is_new = 1; k = key; }
         }
         if (k == key) break;
         slot = (slot + 1) & mask;
-        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrShortFull); return; }
+        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrShortFull); return 0; }
     }
-    atomicAdd(&T.s_counts[slot], delta);
-    u64 inv = ~first_abs;
-    if (__ldcg(&T.s_finv[slot]) < inv) atomicMax(&T.s_finv[slot], inv);
+    atomicAdd(&T.s_counts[slot], delta); // both fire-and-forget (RED)
+    atomicMax(&T.s_finv[slot], ~first_abs);
+    return is_new;
 }
 
 // -------------------------------------------------------- global long table
@@ -207,21 +207,22 @@ __device__ __forceinline__ bool long_equal(const Tables &T, u64 unit, const uint
 }
 
 // A word of 9+ bytes at buf[start, start+len).  Never waits on another thread: a new word is
-// first written to the arena, then published with one CAS of the slot word.
-__device__ __noinline__ void long_insert(const Tables &T, const uint8_t *buf, u64 start, u64 len,
-                                         u64 delta, u64 first_abs, ThreadCounters &tc) {
+// first written to the arena, then published with one CAS of the slot word.  Returns 1 if new.
+__device__ __noinline__ u32 long_insert(const Tables T, const uint8_t *buf, u64 start, u64 len, u64 delta,
+                                        u64 first_abs) {
     const u64 h = long_hash(buf, start, len);
     const u64 mask = (1ull << T.l_log2) - 1;
     const u64 tag = h >> 40;
     u64 slot = h & mask;
     u64 my_ref = 0;
+    u32 is_new = 0;
     for (u32 probes = 0;; ++probes) {
         u64 r = __ldcg(&T.l_refs[slot]);
         if (r == 0) {
             if (my_ref == 0) {
                 u64 units = 1 + ((len + 7) >> 3);
                 u64 idx = atomicAdd(&T.st->arena_used, units);
-                if (idx + units > T.arena_units) { atomicOr(&T.st->err, kErrArenaFull); return; }
+                if (idx + units > T.arena_units) { atomicOr(&T.st->err, kErrArenaFull); return 0; }
                 T.arena[idx] = len;
                 u64 i = 0;
                 for (; i + 8 <= len; i += 8) T.arena[idx + 1 + (i >> 3)] = load8_unaligned(buf, start + i);
@@ -230,15 +231,15 @@ __device__ __noinline__ void long_insert(const Tables &T, const uint8_t *buf, u6
                 my_ref = (tag << 40) | idx;
             }
             r = atomicCAS(&T.l_refs[slot], 0ull, my_ref);
-            if (r == 0) { tc.l_new++; break; }
+            if (r == 0) { is_new = 1; break; }
         }
         if ((r >> 40) == tag && long_equal(T, r & ((1ull << 40) - 1), buf, start, len)) break;
         slot = (slot + 1) & mask;
-        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrLongFull); return; }
+        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrLongFull); return 0; }
     }
     atomicAdd(&T.l_counts[slot], delta);
-    u64 inv = ~first_abs;
-    if (__ldcg(&T.l_finv[slot]) < inv) atomicMax(&T.l_finv[slot], inv);
+    atomicMax(&T.l_finv[slot], ~first_abs);
+    return is_new;
 }
 
 // ------------------------------------------------------------ main kernel
@@ -274,25 +275,95 @@ __device__ __forceinline__ WarpCarry warp_lookback(const uint8_t *buf, u64 pos) 
     return c;
 }
 
-__device__ __forceinline__ uint4 load_tile(const Launch &L, u64 tile, u32 lane) {
-    const u64 off = tile * kTile + (u64)lane * 16;
-    if (off + 16 <= L.n) return __ldcs(reinterpret_cast<const uint4 *>(L.buf + off));
-    u32 w[4] = {0x78787878u, 0x78787878u, 0x78787878u, 0x78787878u}; // past the end: plain word bytes
-    for (u32 i = 0; i < 16 && off + i < L.n; i++) {
-        u32 sh = (i & 3) * 8;
-        w[i >> 2] = (w[i >> 2] & ~(0xFFu << sh)) | ((u32)L.buf[off + i] << sh);
+// 16 bytes at buffer offset `off` (a multiple of 16); bytes at or past n read as 'x' (a word byte).
+__device__ __forceinline__ uint4 load16(const uint8_t *buf, u64 n, u64 off) {
+    if (off + 16 <= n) return __ldcs(reinterpret_cast<const uint4 *>(buf + off));
+    u32 w[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        u32 x = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const u64 i = off + (u64)(j * 4 + b);
+            x |= (i < n ? (u32)buf[i] : 0x78u) << (8 * b);
+        }
+        w[j] = x;
     }
     return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// Fast classification of 4 bytes: cand = byte <= 0x20, lf = 0x0A, ex = a byte <= 0x20 that is
+// neither 0x20 nor 0x0A (0x0D, 0x00, tab, other controls).  In text without such bytes cand is
+// exactly the delimiter set of main.cu:188; a tile that has one takes the exact path below.
+struct FastFlags { u32 cand, lf, ex; };
+__host__ __device__ __forceinline__ FastFlags classify_fast4(u32 x) {
+    const u32 y = x & 0x7F7F7F7Fu;
+    const u32 c = y + 0x5F5F5F5Fu; // bit 7 set <=> low 7 bits >= 0x21
+    FastFlags f;
+    f.cand = ~(c | x) & 0x80808080u;
+    const u32 b = (y ^ 0x0A0A0A0Au) + 0x7F7F7F7Fu;
+    f.lf = ~(b | x) & 0x80808080u;
+    f.ex = f.cand & ~(x << 2) & ~f.lf; // among bytes <= 0x20 only 0x20 has bit 5
+    return f;
+}
+
+// Exact line state of one 512-byte sub-tile: a delimiter flushes only if no
+// 0x0D / 0x00 precedes it on its line.  Taken by tiles that hold a control byte: CRLF files, NULs, tabs.
+struct ExactOut { u32 dm, live, lfm, killed_out; };
+__device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t *buf, u64 n, u64 base,
+                                           u64 sub_off, u64 *stop_ptr, int negate) {
+    const u32 lane = lane_id();
+    const ByteFlags f0 = classify4(v.x), f1 = classify4(v.y), f2 = classify4(v.z), f3 = classify4(v.w);
+    ExactOut o;
+    o.dm = movemask16(f0.delim, f1.delim, f2.delim, f3.delim);
+    o.lfm = movemask16(f0.lf, f1.lf, f2.lf, f3.lf);
+    const u32 km = movemask16(f0.kill, f1.kill, f2.kill, f3.kill);
+    // per-lane transfer function of "killed": s -> reset ? val : (s | val)
+    u32 reset = o.lfm != 0;
+    u32 val = reset ? ((km >> (32 - __clz(o.lfm))) != 0) : (km != 0);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 r2 = __shfl_up_sync(0xFFFFFFFFu, reset, d);
+        const u32 v2 = __shfl_up_sync(0xFFFFFFFFu, val, d);
+        if (lane >= (u32)d) { // compose: earlier (r2, v2) then mine
+            val = reset ? val : (val | v2);
+            reset = reset | r2;
+        }
+    }
+    const u32 r_in = __shfl_up_sync(0xFFFFFFFFu, reset, 1), v_in = __shfl_up_sync(0xFFFFFFFFu, val, 1);
+    bool s = killed_in != 0;
+    if (lane > 0) s = r_in ? (v_in != 0) : (s || v_in);
+    const u32 r_all = __shfl_sync(0xFFFFFFFFu, reset, 31), v_all = __shfl_sync(0xFFFFFFFFu, val, 31);
+    o.killed_out = r_all ? (v_all != 0) : (killed_in || v_all);
+    o.live = 0;
+#pragma unroll
+    for (int p = 0; p < 16; p++) {
+        const u32 bit = 1u << p;
+        if ((o.dm & bit) && !s) o.live |= bit;
+        if (km & bit) s = true;
+        if (o.lfm & bit) s = false;
+    }
+    // A NUL at line offset 0 or 1 makes strlen() < 2: the reference stops (main.cu:185).
+    if (!negate) {
+        u32 nm = km & ~o.dm; // NUL bytes (0x0D is in dm)
+        while (nm) {
+            const u32 p = __ffs(nm) - 1; nm &= nm - 1;
+            const u64 i = sub_off + lane * 16 + p;
+            if (i >= n) break;
+            const bool at0 = i == 0 || buf[i - 1] == 0x0A;
+            const bool at1 = !at0 && (i == 1 || buf[i - 2] == 0x0A);
+            if (at0) atomicMin(stop_ptr, base + i);
+            else if (at1) atomicMin(stop_ptr, base + i - 1);
+        }
+    }
+    return o;
 }
 
 extern __shared__ __align__(16) unsigned char wc_smem[];
 
 __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, const Tables T) {
     uint4 *tab = reinterpret_cast<uint4 *>(wc_smem);
-    u64 *ring_all = reinterpret_cast<u64 *>(wc_smem + kSmemTableBytes);
-    unsigned short *dl_all = reinterpret_cast<unsigned short *>(wc_smem + kSmemTableBytes + kSmemRingBytes);
-    unsigned char *q_all = wc_smem + kSmemTableBytes + kSmemRingBytes + kSmemDlistBytes;
-    __shared__ u32 s_entries;
+    unsigned char *warp_all = wc_smem + kSmemTableBytes;
     __shared__ u32 s_first_ws;
     __shared__ u64 s_stop;
 
@@ -340,42 +411,60 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
     const u64 delta64 = L.negate ? ~0ull : 1ull;
 
     for (u32 i = tid; i < kSmemEntries; i += kThreads) tab[i] = make_uint4(0, 0, 0, 0xFFFFFFFFu);
-    if (tid == 0) s_entries = 0;
     __syncthreads();
 
-    u64 *ring = ring_all + warp * (kRingBytes / 8);
-    unsigned short *dl = dl_all + warp * kTile;
-    u64 *q_start = reinterpret_cast<u64 *>(q_all + warp * (kLongQueue * 12));
-    u32 *q_len = reinterpret_cast<u32 *>(q_all + warp * (kLongQueue * 12) + kLongQueue * 8);
+    // per-warp shared memory: [prev tail 16 B | tile 1024 B | pad] [delimiter list] [spill queue] [long queue]
+    unsigned char *wbase = warp_all + warp * kWarpSmemBytes;
+    uint4 *ring128 = reinterpret_cast<uint4 *>(wbase);
+    const u32 *ring32 = reinterpret_cast<const u32 *>(wbase);
+    unsigned short *dl = reinterpret_cast<unsigned short *>(wbase + kRingBytes);
+    u64 *sq_key = reinterpret_cast<u64 *>(wbase + kRingBytes + kDlBytes);
+    u32 *sq_rel = reinterpret_cast<u32 *>(wbase + kRingBytes + kDlBytes + kQueue * 8);
+    u64 *lq_start = reinterpret_cast<u64 *>(wbase + kRingBytes + kDlBytes + kQueue * 12);
+    u32 *lq_len = reinterpret_cast<u32 *>(wbase + kRingBytes + kDlBytes + kQueue * 12 + kQueue * 8);
 
     const u64 tiles_total = (L.n + kTile - 1) / kTile;
     const u64 gwarp = (u64)blockIdx.x * kWarps + warp;
     u64 t0 = gwarp * L.tiles_per_warp;
-    u64 t1 = t0 + L.tiles_per_warp < tiles_total ? t0 + L.tiles_per_warp : tiles_total;
+    const u64 t1 = t0 + L.tiles_per_warp < tiles_total ? t0 + L.tiles_per_warp : tiles_total;
     const u64 cta_base = (u64)blockIdx.x * kWarps * L.tiles_per_warp * kTile; // buffer-relative
     if (range_lo > 0 && t0 < t1) { // roll-back: start at the tile that holds range_lo
-        u64 tl = range_lo / kTile;
+        const u64 tl = range_lo / kTile;
         if (tl >= t1) t0 = t1; else if (tl > t0) t0 = tl;
     }
 
-    ThreadCounters tc = {0, 0, 0, 0};
-    u64 acc_flush = 0, acc_empty = 0, acc_slow = 0;
-    u32 q_count = 0;
-    bool seen_nonempty = false;
-    u64 my_p0 = kNone, my_empties_before = 0;
+    u32 n_snew = 0, n_lnew = 0, n_long = 0, n_spill = 0;
+    u32 acc_flush = 0, acc_empty = 0, acc_slow = 0; // per lane; a warp's range is < 4 GiB
+    u32 sq_count = 0, lq_count = 0;
+    bool seen_nonempty = L.negate != 0; // roll-back launches do not look for P0
+    u64 my_p0 = kNone;
+    u32 my_empties_before = 0;
 
-    // Drain up to 32 queued long words, one per lane.
+    // Queued work is done 32 entries at a time so that every lane has a global-memory access in
+    // flight at once instead of the whole warp waiting on two or three.
+    auto drain_spill = [&](u32 take) {
+        if (lane < take) n_snew += gs_insert(T, sq_key[lane], delta64, L.base + cta_base + sq_rel[lane]);
+        __syncwarp();
+        u64 mk = 0; u32 mr = 0;
+        const bool mv = lane + take < sq_count;
+        if (mv) { mk = sq_key[lane + take]; mr = sq_rel[lane + take]; }
+        __syncwarp();
+        if (mv) { sq_key[lane] = mk; sq_rel[lane] = mr; }
+        sq_count -= take;
+        __syncwarp();
+    };
     auto drain_long = [&](u32 take) {
         if (lane < take) {
-            u64 s = q_start[lane]; u64 l = q_len[lane];
-            long_insert(T, L.buf, s, l, delta64, L.base + s + l, tc);
+            const u64 s = lq_start[lane], l = lq_len[lane];
+            n_lnew += long_insert(T, L.buf, s, l, delta64, L.base + s + l);
         }
         __syncwarp();
         u64 ms = 0; u32 ml = 0;
-        if (lane + take < q_count) { ms = q_start[lane + take]; ml = q_len[lane + take]; }
+        const bool mv = lane + take < lq_count;
+        if (mv) { ms = lq_start[lane + take]; ml = lq_len[lane + take]; }
         __syncwarp();
-        if (lane + take < q_count) { q_start[lane] = ms; q_len[lane] = ml; }
-        q_count -= take;
+        if (mv) { lq_start[lane] = ms; lq_len[lane] = ml; }
+        lq_count -= take;
         __syncwarp();
     };
 
@@ -384,237 +473,247 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
         if (t0 == 0) { carry.last_delim = -1; carry.killed = false; carry.last_is_lf = true; }
         else {
             carry = warp_lookback(L.buf, t0 * kTile);
-            reinterpret_cast<uint4 *>(ring)[((t0 - 1) & 1) * 32 + lane] = load_tile(L, t0 - 1, lane);
+            if (lane == 0) ring128[0] = load16(L.buf, L.n, t0 * kTile - 16);
         }
-        uint4 vnext = load_tile(L, t0, lane);
+        uint4 na = load16(L.buf, L.n, t0 * kTile + lane * 16);
+        uint4 nb = load16(L.buf, L.n, t0 * kTile + kSub + lane * 16);
         for (u64 t = t0; t < t1; ++t) {
-            const uint4 v = vnext;
-            if (t + 1 < t1) vnext = load_tile(L, t + 1, lane);
+            const uint4 va = na, vb = nb;
+            if (t + 1 < t1) {
+                na = load16(L.buf, L.n, (t + 1) * kTile + lane * 16);
+                nb = load16(L.buf, L.n, (t + 1) * kTile + kSub + lane * 16);
+            }
             const u64 T0 = t * kTile; // buffer-relative offset of this tile
-            reinterpret_cast<uint4 *>(ring)[(t & 1) * 32 + lane] = v;
+            ring128[1 + lane] = va;
+            ring128[33 + lane] = vb;
 
-            // ---- classify 16 bytes
-            ByteFlags f0 = classify4(v.x), f1 = classify4(v.y), f2 = classify4(v.z), f3 = classify4(v.w);
-            u32 dm = movemask16(f0.delim, f1.delim, f2.delim, f3.delim);
-            u32 lfm = movemask16(f0.lf, f1.lf, f2.lf, f3.lf);
-            const bool special = (f0.kill | f1.kill | f2.kill | f3.kill) != 0;
-            u32 live = dm; // delimiters that flush a word
-            const u32 prev_lf_in = __shfl_up_sync(0xFFFFFFFFu, lfm >> 15, 1);
-            const u32 prev_lf = lane == 0 ? (carry.last_is_lf ? 1u : 0u) : prev_lf_in;
-
-            if (__any_sync(0xFFFFFFFFu, special) || carry.killed) {
-                // ---- exact line state: a delimiter flushes only if no 0x0D / 0x00
-                // precedes it on its line.  Rare: CRLF files, stray NULs.
-                acc_slow += lane == 0;
-                const u32 km = movemask16(f0.kill, f1.kill, f2.kill, f3.kill);
-                // per-lane transfer function of "killed": s -> reset ? val : (s | val)
-                u32 reset = lfm != 0;
-                u32 val = reset ? ((km >> (32 - __clz(lfm))) != 0) : (km != 0);
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    u32 r2 = __shfl_up_sync(0xFFFFFFFFu, reset, d);
-                    u32 v2 = __shfl_up_sync(0xFFFFFFFFu, val, d);
-                    if (lane >= (u32)d) { // compose: earlier (r2, v2) then mine
-                        val = reset ? val : (val | v2);
-                        reset = reset | r2;
-                    }
+            // ---- classify 2 x 16 bytes
+            u32 dmA, dmB, lfA, lfB, liveA, liveB;
+            {
+                const FastFlags a0 = classify_fast4(va.x), a1 = classify_fast4(va.y), a2 = classify_fast4(va.z),
+                                a3 = classify_fast4(va.w);
+                const FastFlags b0 = classify_fast4(vb.x), b1 = classify_fast4(vb.y), b2 = classify_fast4(vb.z),
+                                b3 = classify_fast4(vb.w);
+                dmA = movemask16(a0.cand, a1.cand, a2.cand, a3.cand);
+                dmB = movemask16(b0.cand, b1.cand, b2.cand, b3.cand);
+                lfA = movemask16(a0.lf, a1.lf, a2.lf, a3.lf);
+                lfB = movemask16(b0.lf, b1.lf, b2.lf, b3.lf);
+                const u32 ex = a0.ex | a1.ex | a2.ex | a3.ex | b0.ex | b1.ex | b2.ex | b3.ex;
+                liveA = dmA; liveB = dmB;
+                if (__any_sync(0xFFFFFFFFu, ex != 0) || carry.killed) {
+                    acc_slow += lane == 0;
+                    const ExactOut oa = exact_sub(va, carry.killed, L.buf, L.n, L.base, T0, &st->stop, L.negate);
+                    const ExactOut ob = exact_sub(vb, oa.killed_out, L.buf, L.n, L.base, T0 + kSub, &st->stop, L.negate);
+                    dmA = oa.dm; liveA = oa.live; lfA = oa.lfm;
+                    dmB = ob.dm; liveB = ob.live; lfB = ob.lfm;
+                    carry.killed = ob.killed_out != 0;
                 }
-                // state entering this lane = transfer of lanes < lane applied to the carry
-                u32 r_in = __shfl_up_sync(0xFFFFFFFFu, reset, 1), v_in = __shfl_up_sync(0xFFFFFFFFu, val, 1);
-                bool s = carry.killed;
-                if (lane > 0) s = r_in ? (v_in != 0) : (s || v_in);
-                const u32 r_all = __shfl_sync(0xFFFFFFFFu, reset, 31), v_all = __shfl_sync(0xFFFFFFFFu, val, 31);
-                const bool killed_out = r_all ? (v_all != 0) : (carry.killed || v_all);
-                live = 0;
-#pragma unroll
-                for (int p = 0; p < 16; p++) {
-                    const u32 bit = 1u << p;
-                    if ((dm & bit) && !s) live |= bit;
-                    if (km & bit) s = true;
-                    if (lfm & bit) s = false;
-                }
-                // A NUL at line offset 0 or 1 makes strlen() < 2: the reference stops (main.cu:185).
-                if (!L.negate) {
-                    u32 nm = km & ~dm; // NUL bytes (0x0D is in dm)
-                    while (nm) {
-                        const u32 p = __ffs(nm) - 1; nm &= nm - 1;
-                        const u64 i = T0 + lane * 16 + p;
-                        if (i >= L.n) break;
-                        const bool at0 = i == 0 || L.buf[i - 1] == 0x0A;
-                        const bool at1 = !at0 && (i == 1 || L.buf[i - 2] == 0x0A);
-                        if (at0) atomicMin(&st->stop, L.base + i);
-                        else if (at1) atomicMin(&st->stop, L.base + i - 1);
-                    }
-                }
-                carry.killed = killed_out;
             }
 
             // ---- STOP: a line that is just "\n" (main.cu:185), or a 1-byte tail at the very end
-            if (!L.negate) {
-                const u32 at_line_start = ((lfm << 1) | prev_lf) & 0xFFFFu; // bit p: byte p starts a line
-                const u32 blank = lfm & at_line_start;
-                if (blank) atomicMin(&st->stop, L.base + T0 + lane * 16 + (__ffs(blank) - 1));
-                if (L.last_piece && L.n - 1 >= T0 + lane * 16 && L.n - 1 < T0 + lane * 16 + 16) {
-                    const u32 p = (u32)(L.n - 1 - (T0 + lane * 16));
-                    if ((at_line_start >> p) & 1) atomicMin(&st->stop, L.base + L.n - 1);
+            {
+                const u32 lastA = __shfl_sync(0xFFFFFFFFu, lfA >> 15, 31);
+                const u32 upA = __shfl_up_sync(0xFFFFFFFFu, lfA >> 15, 1), upB = __shfl_up_sync(0xFFFFFFFFu, lfB >> 15, 1);
+                const u32 prevA = lane == 0 ? (carry.last_is_lf ? 1u : 0u) : upA;
+                const u32 prevB = lane == 0 ? lastA : upB;
+                if (!L.negate) {
+                    const u32 startA = ((lfA << 1) | prevA) & 0xFFFFu, startB = ((lfB << 1) | prevB) & 0xFFFFu;
+                    const u32 blankA = lfA & startA, blankB = lfB & startB; // bit p: byte p starts a line
+                    if (blankA) atomicMin(&st->stop, L.base + T0 + lane * 16 + (__ffs(blankA) - 1));
+                    if (blankB) atomicMin(&st->stop, L.base + T0 + kSub + lane * 16 + (__ffs(blankB) - 1));
+                    if (L.last_piece && L.n - 1 >= T0 && L.n - 1 < T0 + kTile) {
+                        const u32 q = (u32)(L.n - 1 - T0); // position of the last byte in this tile
+                        const u32 own = q & 511, p = own & 15;
+                        const u32 starts = q < kSub ? startA : startB;
+                        if ((own >> 4) == lane && ((starts >> p) & 1)) atomicMin(&st->stop, L.base + L.n - 1);
+                    }
                 }
+                carry.last_is_lf = __shfl_sync(0xFFFFFFFFu, lfB >> 15, 31) != 0;
             }
-            carry.last_is_lf = __shfl_sync(0xFFFFFFFFu, lfm >> 15, 31) != 0;
 
             // Roll-back launches only see flush points at or after range_lo.
             if (range_lo > T0) {
-                const u64 lane_lo = T0 + lane * 16;
-                if (range_lo >= lane_lo + 16) live = 0;
-                else if (range_lo > lane_lo) live &= ~((1u << (u32)(range_lo - lane_lo)) - 1);
+                const u64 loA = T0 + lane * 16, loB = loA + kSub;
+                if (range_lo >= loA + 16) liveA = 0;
+                else if (range_lo > loA) liveA &= ~((1u << (u32)(range_lo - loA)) - 1);
+                if (range_lo >= loB + 16) liveB = 0;
+                else if (range_lo > loB) liveB &= ~((1u << (u32)(range_lo - loB)) - 1);
             }
+            acc_flush += __popc(liveA) + __popc(liveB);
 
-            // ---- list every delimiter of the tile in position order
-            const u32 cnt = __popc(dm);
-            const u32 incl = warp_incl_scan(cnt);
-            const u32 total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-            {
-                u32 idx = incl - cnt, m = dm;
-                while (m) {
-                    const u32 p = __ffs(m) - 1; m &= m - 1;
-                    dl[idx++] = (unsigned short)((lane * 16 + p) | (((live >> p) & 1u) << 15));
+            // ---- position-ordered list of every delimiter; one scan serves both sub-tiles
+            const u32 cntA = __popc(dmA), cntB = __popc(dmB);
+            const u32 incl = warp_incl_scan(cntA | (cntB << 16));
+            const u32 tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
+            const u32 totA = tot & 0xFFFFu, totB = tot >> 16;
+            const u32 exclA = (incl & 0xFFFFu) - cntA, exclB = (incl >> 16) - cntB;
+            const u32 relT = (u32)(T0 - cta_base);
+
+            // The list holds at most kDlCap entries: a tile dense with delimiters is done one sub-tile
+            // at a time.  `first_prev` is the position (tile relative, negative if it lies before the
+            // tile) of the delimiter that precedes list entry 0.
+            long long cr = carry.last_delim - (long long)T0; // <= -1
+            int first_prev = cr < -4096 ? -4096 : (int)cr;
+            const bool dense = totA + totB > (u32)kDlCap;
+            for (int ph = 0; ph < (dense ? 2 : 1); ph++) {
+                if (!dense || ph == 0) {
+                    u32 idx = exclA, m = dmA;
+                    while (m) {
+                        const u32 p = __ffs(m) - 1; m &= m - 1;
+                        dl[idx++] = (unsigned short)((lane * 16 + p) | (((liveA >> p) & 1u) << 15));
+                    }
                 }
-            }
-            acc_flush += __popc(live);
-            __syncwarp();
-
-            // ---- one word per lane
-            const long long carry_rel = carry.last_delim - (long long)T0; // <= -1
-            for (u32 k0 = 0; k0 < total; k0 += 32) {
-                const u32 k = k0 + lane;
-                const bool valid = k < total;
-                const u32 d = valid ? dl[k] : 0;
-                const int e = (int)(d & 0x1FFu);
-                const bool flushes = valid && (d >> 15);
-                const u32 d_up = __shfl_up_sync(0xFFFFFFFFu, d, 1);
-                long long prev;
-                if (lane > 0) prev = (long long)(d_up & 0x1FFu);
-                else prev = k > 0 ? (long long)(dl[k - 1] & 0x1FFu) : carry_rel;
-                const long long len = (long long)e - prev - 1;
-                const bool nonempty = flushes && len > 0;
-                const bool empty = flushes && len == 0;
-                acc_empty += empty;
-
-                if (!seen_nonempty && !L.negate) { // still looking for this warp's first non-empty word
-                    const u32 bn = __ballot_sync(0xFFFFFFFFu, nonempty);
-                    const u32 be = __ballot_sync(0xFFFFFFFFu, empty);
-                    if (bn) {
-                        const u32 fl = __ffs(bn) - 1;
-                        my_empties_before += __popc(be & ((1u << fl) - 1));
-                        my_p0 = L.base + T0 + (u64)__shfl_sync(0xFFFFFFFFu, e, fl);
-                        seen_nonempty = true;
-                    } else my_empties_before += __popc(be);
+                if (!dense || ph == 1) {
+                    u32 idx = (dense ? 0u : totA) + exclB, m = dmB;
+                    while (m) {
+                        const u32 p = __ffs(m) - 1; m &= m - 1;
+                        dl[idx++] = (unsigned short)((kSub + lane * 16 + p) | (((liveB >> p) & 1u) << 15));
+                    }
                 }
+                __syncwarp();
+                const u32 total = dense ? (ph ? totB : totA) : totA + totB;
+                // ---- one word per lane
+                for (u32 k0 = 0; k0 < total; k0 += 32) {
+                    const u32 k = k0 + lane;
+                    const u32 d = k < total ? (u32)dl[k] : 0u;
+                    const u32 d_up = __shfl_up_sync(0xFFFFFFFFu, d, 1);
+                    const int e = (int)(d & 0x3FFu);
+                    int prev = (int)(d_up & 0x3FFu);
+                    if (lane == 0) prev = k0 ? (int)(dl[k0 - 1] & 0x3FFu) : first_prev;
+                    const int len = e - prev - 1;
+                    const bool flushes = (d >> 15) != 0;
+                    const bool nonempty = flushes && len > 0;
+                    if (flushes && len == 0) acc_empty++;
 
-                const bool is_long = nonempty && len > 8;
-                if (nonempty && !is_long) {
-                    // ---- key = the word's bytes, from the shared-memory copy of this and the previous tile
-                    const int s = e - (int)len; // >= -8
-                    const u32 ridx = (u32)(((int)((t & 1) << 9) + s) & (kRingBytes - 1));
-                    const u32 sh = (ridx & 7) * 8;
-                    u64 key = ring[ridx >> 3] >> sh;
-                    if ((ridx & 7) + (u32)len > 8) key |= ring[((ridx >> 3) + 1) & (kRingBytes / 8 - 1)] << (64 - sh);
-                    if (len < 8) key &= (1ull << (8 * (u32)len)) - 1;
-                    const u32 klo = (u32)key, khi = (u32)(key >> 32);
-                    const u32 rel = (u32)(T0 + (u64)e - cta_base);
+                    if (!seen_nonempty) { // still looking for this warp's first non-empty word
+                        const u32 bn = __ballot_sync(0xFFFFFFFFu, nonempty);
+                        const u32 be = __ballot_sync(0xFFFFFFFFu, flushes && len == 0);
+                        if (bn) {
+                            const u32 fl = __ffs(bn) - 1;
+                            my_empties_before += __popc(be & ((1u << fl) - 1));
+                            my_p0 = L.base + T0 + (u64)__shfl_sync(0xFFFFFFFFu, e, fl);
+                            seen_nonempty = true;
+                        } else my_empties_before += __popc(be);
+                    }
 
-                    u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);
-                    bool done = false;
-#pragma unroll 1
-                    for (int probe = 0; probe < kSmemMaxProbe; ++probe) {
+                    const bool is_long = nonempty && len > 8;
+                    bool spill = false;
+                    u32 klo = 0, khi = 0;
+                    const u32 rel = relT + (u32)e;
+                    if (nonempty && !is_long) {
+                        // ---- key = the word's bytes, from the warp's shared-memory copy of the tile
+                        const u32 idx = (u32)(16 + e - len); // >= 8: reaches into the previous tile's tail
+                        const u32 *r = ring32 + (idx >> 2);
+                        const u32 w0 = r[0], w1 = r[1], w2 = r[2];
+                        const u32 sh = (idx & 3) * 8;
+                        klo = __funnelshift_r(w0, w1, sh);
+                        khi = __funnelshift_r(w1, w2, sh);
+                        const u64 m = ~0ull >> (64 - 8 * len);
+                        klo &= (u32)m; khi &= (u32)(m >> 32);
+
+                        // ---- single-probe shared-memory table: hit, claim an empty slot, or spill
+                        const u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);
                         uint4 ent = tab[slot];
-                        if (ent.x == klo && ent.y == khi) done = true;
-                        else if ((ent.x | ent.y) == 0) {
-                            if (*reinterpret_cast<volatile u32 *>(&s_entries) >= kSmemLimit) break;
+                        bool hit = ent.x == klo && ent.y == khi;
+                        if (!hit && (ent.x | ent.y) == 0) {
+                            const u64 key = (u64)klo | ((u64)khi << 32);
                             const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[slot]), 0ull, key);
-                            if (old == 0) { atomicAdd(&s_entries, 1u); done = true; }
-                            else if (old == key) done = true;
+                            hit = old == 0 || old == key;
                             ent.w = 0xFFFFFFFFu;
                         }
-                        if (done) {
+                        if (hit) {
                             u32 *cell = reinterpret_cast<u32 *>(&tab[slot]);
                             atomicAdd(cell + 2, delta32);
                             if (rel < ent.w) atomicMin(cell + 3, rel);
-                            break;
                         }
-                        slot = slot + 1 == kSmemEntries ? 0 : slot + 1;
+                        spill = !hit;
                     }
-                    if (!done) { // table full or a long probe chain: count in the global table
-                        tc.n_spill++;
-                        gs_insert(T, key, delta64, L.base + T0 + (u64)e, tc);
-                    }
-                }
 
-                // ---- words of 9+ bytes are queued and handled 32 at a time
-                const u32 bl = __ballot_sync(0xFFFFFFFFu, is_long);
-                if (bl) {
-                    if (is_long) {
-                        const u32 qi = q_count + __popc(bl & ((1u << lane) - 1));
-                        const long long start = (long long)T0 + prev + 1;
-                        q_start[qi] = (u64)start;
-                        if (len > 0x7FFFFFFFll) { atomicOr(&st->err, kErrWordTooLong); q_len[qi] = 9; }
-                        else q_len[qi] = (u32)len;
-                        tc.n_long++;
+                    // ---- words the table has no room for, and words of 9+ bytes, are queued
+                    const u32 bs = __ballot_sync(0xFFFFFFFFu, spill);
+                    if (bs) {
+                        if (spill) {
+                            const u32 qi = sq_count + __popc(bs & ((1u << lane) - 1));
+                            sq_key[qi] = (u64)klo | ((u64)khi << 32);
+                            sq_rel[qi] = rel;
+                        }
+                        sq_count += __popc(bs);
+                        n_spill += spill;
+                        __syncwarp();
+                        if (sq_count >= 32) drain_spill(32);
                     }
-                    q_count += __popc(bl);
-                    __syncwarp();
-                    if (q_count >= 32) drain_long(32);
+                    const u32 bl = __ballot_sync(0xFFFFFFFFu, is_long);
+                    if (bl) {
+                        if (is_long) {
+                            const u32 qi = lq_count + __popc(bl & ((1u << lane) - 1));
+                            // entry 0's word may start far back: its true start is the carried delimiter + 1
+                            const long long start = (k == 0 && first_prev < 0) ? carry.last_delim + 1
+                                                                               : (long long)T0 + prev + 1;
+                            const long long wl = (long long)T0 + e - start;
+                            lq_start[qi] = (u64)start;
+                            if (wl > 0x7FFFFFFFll) { atomicOr(&st->err, kErrWordTooLong); lq_len[qi] = 9; }
+                            else lq_len[qi] = (u32)wl;
+                            n_long++;
+                        }
+                        lq_count += __popc(bl);
+                        __syncwarp();
+                        if (lq_count >= 32) drain_long(32);
+                    }
                 }
+                if (total > 0) {
+                    first_prev = (int)(dl[total - 1] & 0x3FFu);
+                    carry.last_delim = (long long)T0 + first_prev;
+                }
+                __syncwarp();
             }
-            if (total > 0) carry.last_delim = (long long)T0 + (long long)(dl[total - 1] & 0x1FFu);
+            __syncwarp();
+            if (lane == 31) ring128[0] = vb; // the next tile's words may start in this tile's last bytes
             __syncwarp();
         }
-        if (q_count > 0) drain_long(q_count);
+        if (sq_count > 0) drain_spill(sq_count);
+        if (lq_count > 0) drain_long(lq_count);
     }
 
     // ---- per-warp results
-    acc_flush = warp_sum64(acc_flush);
-    acc_empty = warp_sum64(acc_empty);
-    const u32 w_snew = __reduce_add_sync(0xFFFFFFFFu, tc.s_new), w_lnew = __reduce_add_sync(0xFFFFFFFFu, tc.l_new);
-    const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, tc.n_long), w_spill = __reduce_add_sync(0xFFFFFFFFu, tc.n_spill);
+    const u64 w_flush = warp_sum64(acc_flush), w_empty = warp_sum64(acc_empty);
+    const u32 w_lnew = __reduce_add_sync(0xFFFFFFFFu, n_lnew);
+    const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, n_long), w_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
     if (lane == 0) {
-        if (acc_flush) atomicAdd(&st->n_flush, L.negate ? (u64)(-(long long)acc_flush) : acc_flush);
-        if (acc_empty) atomicAdd(&st->n_empty, L.negate ? (u64)(-(long long)acc_empty) : acc_empty);
-        if (w_snew) atomicAdd(&st->s_entries, (u64)w_snew);
+        if (w_flush) atomicAdd(&st->n_flush, L.negate ? (u64)(-(long long)w_flush) : w_flush);
+        if (w_empty) atomicAdd(&st->n_empty, L.negate ? (u64)(-(long long)w_empty) : w_empty);
         if (w_lnew) atomicAdd(&st->l_entries, (u64)w_lnew);
         if (!L.negate) {
             if (w_long) atomicAdd(&st->n_long, (u64)w_long);
             if (w_spill) atomicAdd(&st->n_spill, (u64)w_spill);
-            if (acc_slow) atomicAdd(&st->n_slow_tiles, acc_slow);
+            if (acc_slow) atomicAdd(&st->n_slow_tiles, (u64)acc_slow);
             if (L.ws != nullptr && gwarp < L.n_ws) {
                 L.ws[gwarp].p0 = my_p0;
                 L.ws[gwarp].empties_before = my_empties_before;
-                L.ws[gwarp].empties_total = acc_empty;
+                L.ws[gwarp].empties_total = w_empty;
             }
         }
     }
 
     // ---- flush the CTA's table into the global one
     __syncthreads();
-    ThreadCounters fc = {0, 0, 0, 0};
     for (u32 i = tid; i < kSmemEntries; i += kThreads) {
         const uint4 ent = tab[i];
         if ((ent.x | ent.y) != 0 && ent.z != 0) {
             const u64 key = (u64)ent.x | ((u64)ent.y << 32);
-            gs_insert(T, key, (u64)(long long)(int)ent.z, L.base + cta_base + ent.w, fc);
+            n_snew += gs_insert(T, key, (u64)(long long)(int)ent.z, L.base + cta_base + ent.w);
         }
     }
-    const u32 f_new = __reduce_add_sync(0xFFFFFFFFu, fc.s_new);
-    if (lane == 0 && f_new) atomicAdd(&st->s_entries, (u64)f_new);
+    const u32 w_snew = __reduce_add_sync(0xFFFFFFFFu, n_snew);
+    if (lane == 0 && w_snew) atomicAdd(&st->s_entries, (u64)w_snew);
 }
 
 // ------------------------------------------------------------ table growth
 
 __global__ void rehash_short_kernel(const u64 *keys, const u64 *counts, const u64 *finv, u64 n_old, Tables T) {
-    ThreadCounters tc = {0, 0, 0, 0};
     for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n_old; i += (u64)gridDim.x * blockDim.x) {
         const u64 k = keys[i];
         if (k == 0) continue;
-        gs_insert(T, k, counts[i], ~finv[i], tc);
+        gs_insert(T, k, counts[i], ~finv[i]);
     }
 }
 
