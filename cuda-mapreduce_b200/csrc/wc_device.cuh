@@ -22,14 +22,14 @@ constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 
 constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = 16;                 // warps per CTA
 constexpr int kThreads = kWarps * 32;
-constexpr u32 kSmemEntries = 10880;        // 16-byte entries of the per-CTA table (170 KiB)
+constexpr u32 kSmemEntries = 11904;        // 16-byte entries of the per-CTA table (186 KiB)
 constexpr int kRingBytes = 1072;           // per warp: 16 B tail of the previous tile + the tile + slack
 constexpr int kDlCap = 512;                // per warp: delimiter list entries
 constexpr int kDlBytes = kDlCap * 2;
-constexpr int kQueue = 64;                 // per warp: pending spilled words / pending long words
+constexpr int kQueue = 64;                 // per warp: deferred words (8-byte records)
 constexpr u64 kNone = ~0ull;
 
-constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + 2 * kQueue * 12;
+constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kQueue * 8;
 constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16;
 constexpr size_t kSmemTotal = kSmemTableBytes + (size_t)kWarps * kWarpSmemBytes;
 static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
@@ -359,9 +359,36 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
     return o;
 }
 
+// Deferred words: short words the CTA's table had no room for, and every word of 9+ bytes.  A
+// record is (end offset relative to the CTA's range, length).  They are inserted into the global
+// tables 32 at a time, so that every lane has its global-memory accesses in flight at once instead
+// of the whole warp waiting on two or three.  Returns new short slots | new long slots << 16.
+__device__ __noinline__ u32 drain_deferred(uint2 *q, u32 count, u32 take, const Launch *Lp, const Tables *Tp,
+                                           u64 cta_base) {
+    const u32 lane = lane_id();
+    u32 made = 0;
+    if (lane < take) {
+        const uint2 rec = q[lane];
+        const u64 end = cta_base + rec.x;      // buffer-relative offset of the delimiter
+        const u64 start = end - rec.y;
+        const u64 delta = Lp->negate ? ~0ull : 1ull;
+        if (rec.y <= 8) made = gs_insert(*Tp, load8_unaligned(Lp->buf, start, rec.y), delta, Lp->base + end);
+        else made = long_insert(*Tp, Lp->buf, start, rec.y, delta, Lp->base + end) << 16;
+    }
+    __syncwarp();
+    uint2 mv = make_uint2(0, 0);
+    const bool keep = lane + take < count;
+    if (keep) mv = q[lane + take];
+    __syncwarp();
+    if (keep) q[lane] = mv;
+    __syncwarp();
+    return made;
+}
+
 extern __shared__ __align__(16) unsigned char wc_smem[];
 
-__global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, const Tables T) {
+__global__ void __launch_bounds__(kThreads, 1)
+count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T) {
     uint4 *tab = reinterpret_cast<uint4 *>(wc_smem);
     unsigned char *warp_all = wc_smem + kSmemTableBytes;
     __shared__ u32 s_first_ws;
@@ -408,82 +435,57 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
         }
     }
     const u32 delta32 = L.negate ? 0xFFFFFFFFu : 1u;
-    const u64 delta64 = L.negate ? ~0ull : 1ull;
 
     for (u32 i = tid; i < kSmemEntries; i += kThreads) tab[i] = make_uint4(0, 0, 0, 0xFFFFFFFFu);
     __syncthreads();
 
-    // per-warp shared memory: [prev tail 16 B | tile 1024 B | pad] [delimiter list] [spill queue] [long queue]
+    // per-warp shared memory: [prev tail 16 B | tile 1024 B | slack] [delimiter list] [deferred queue]
     unsigned char *wbase = warp_all + warp * kWarpSmemBytes;
     uint4 *ring128 = reinterpret_cast<uint4 *>(wbase);
     const u32 *ring32 = reinterpret_cast<const u32 *>(wbase);
     unsigned short *dl = reinterpret_cast<unsigned short *>(wbase + kRingBytes);
-    u64 *sq_key = reinterpret_cast<u64 *>(wbase + kRingBytes + kDlBytes);
-    u32 *sq_rel = reinterpret_cast<u32 *>(wbase + kRingBytes + kDlBytes + kQueue * 8);
-    u64 *lq_start = reinterpret_cast<u64 *>(wbase + kRingBytes + kDlBytes + kQueue * 12);
-    u32 *lq_len = reinterpret_cast<u32 *>(wbase + kRingBytes + kDlBytes + kQueue * 12 + kQueue * 8);
+    uint2 *dq = reinterpret_cast<uint2 *>(wbase + kRingBytes + kDlBytes);
 
-    const u64 tiles_total = (L.n + kTile - 1) / kTile;
-    const u64 gwarp = (u64)blockIdx.x * kWarps + warp;
-    u64 t0 = gwarp * L.tiles_per_warp;
-    const u64 t1 = t0 + L.tiles_per_warp < tiles_total ? t0 + L.tiles_per_warp : tiles_total;
+    const u32 tiles_total = (u32)((L.n + kTile - 1) / kTile);
+    const u32 gwarp = blockIdx.x * kWarps + warp;
+    u32 t0 = gwarp * L.tiles_per_warp < tiles_total ? gwarp * L.tiles_per_warp : tiles_total;
+    const u32 t1 = t0 + L.tiles_per_warp < tiles_total ? t0 + L.tiles_per_warp : tiles_total;
     const u64 cta_base = (u64)blockIdx.x * kWarps * L.tiles_per_warp * kTile; // buffer-relative
     if (range_lo > 0 && t0 < t1) { // roll-back: start at the tile that holds range_lo
         const u64 tl = range_lo / kTile;
-        if (tl >= t1) t0 = t1; else if (tl > t0) t0 = tl;
+        if (tl >= t1) t0 = t1; else if (tl > t0) t0 = (u32)tl;
     }
+    const u32 lt_mask = (1u << lane) - 1;
 
-    u32 n_snew = 0, n_lnew = 0, n_long = 0, n_spill = 0;
-    u32 acc_flush = 0, acc_empty = 0, acc_slow = 0; // per lane; a warp's range is < 4 GiB
-    u32 sq_count = 0, lq_count = 0;
-    bool seen_nonempty = L.negate != 0; // roll-back launches do not look for P0
-    u64 my_p0 = kNone;
-    u32 my_empties_before = 0;
-
-    // Queued work is done 32 entries at a time so that every lane has a global-memory access in
-    // flight at once instead of the whole warp waiting on two or three.
-    auto drain_spill = [&](u32 take) {
-        if (lane < take) n_snew += gs_insert(T, sq_key[lane], delta64, L.base + cta_base + sq_rel[lane]);
-        __syncwarp();
-        u64 mk = 0; u32 mr = 0;
-        const bool mv = lane + take < sq_count;
-        if (mv) { mk = sq_key[lane + take]; mr = sq_rel[lane + take]; }
-        __syncwarp();
-        if (mv) { sq_key[lane] = mk; sq_rel[lane] = mr; }
-        sq_count -= take;
-        __syncwarp();
-    };
-    auto drain_long = [&](u32 take) {
-        if (lane < take) {
-            const u64 s = lq_start[lane], l = lq_len[lane];
-            n_lnew += long_insert(T, L.buf, s, l, delta64, L.base + s + l);
-        }
-        __syncwarp();
-        u64 ms = 0; u32 ml = 0;
-        const bool mv = lane + take < lq_count;
-        if (mv) { ms = lq_start[lane + take]; ml = lq_len[lane + take]; }
-        __syncwarp();
-        if (mv) { lq_start[lane] = ms; lq_len[lane] = ml; }
-        lq_count -= take;
-        __syncwarp();
-    };
+    u32 n_made = 0;                                  // new global slots: short | long << 16
+    u32 n_long = 0, n_spill = 0;
+    u32 acc_flush = 0, acc_empty = 0, acc_slow = 0;  // per lane; a warp's range is < 4 GiB
+    u32 q_count = 0;
+    bool seen_nonempty = L.negate != 0;              // roll-back launches do not look for P0
+    u32 p0_rel = 0, my_empties_before = 0;           // P0 relative to cta_base
 
     if (t0 < t1) {
-        WarpCarry carry;
-        if (t0 == 0) { carry.last_delim = -1; carry.killed = false; carry.last_is_lf = true; }
+        // carry from tile to tile: position of the last delimiter (relative to the NEXT tile's start,
+        // so always negative), the line state, and whether the previous byte was a line feed
+        int carry_prev; bool killed, last_is_lf;
+        if (t0 == 0) { carry_prev = -1; killed = false; last_is_lf = true; }
         else {
-            carry = warp_lookback(L.buf, t0 * kTile);
-            if (lane == 0) ring128[0] = load16(L.buf, L.n, t0 * kTile - 16);
+            const WarpCarry c = warp_lookback(L.buf, (u64)t0 * kTile);
+            const long long cr = c.last_delim - (long long)t0 * kTile;
+            carry_prev = cr < -(1ll << 30) ? -(1 << 30) : (int)cr;
+            killed = c.killed; last_is_lf = c.last_is_lf;
+            if (lane == 0) ring128[0] = load16(L.buf, L.n, (u64)t0 * kTile - 16);
         }
-        uint4 na = load16(L.buf, L.n, t0 * kTile + lane * 16);
-        uint4 nb = load16(L.buf, L.n, t0 * kTile + kSub + lane * 16);
-        for (u64 t = t0; t < t1; ++t) {
+        uint4 na = load16(L.buf, L.n, (u64)t0 * kTile + lane * 16);
+        uint4 nb = load16(L.buf, L.n, (u64)t0 * kTile + kSub + lane * 16);
+        for (u32 t = t0; t < t1; ++t) {
             const uint4 va = na, vb = nb;
             if (t + 1 < t1) {
-                na = load16(L.buf, L.n, (t + 1) * kTile + lane * 16);
-                nb = load16(L.buf, L.n, (t + 1) * kTile + kSub + lane * 16);
+                na = load16(L.buf, L.n, (u64)(t + 1) * kTile + lane * 16);
+                nb = load16(L.buf, L.n, (u64)(t + 1) * kTile + kSub + lane * 16);
             }
-            const u64 T0 = t * kTile; // buffer-relative offset of this tile
+            const u64 T0 = (u64)t * kTile;          // buffer-relative offset of this tile
+            const u32 relT = (u32)(T0 - cta_base);
             ring128[1 + lane] = va;
             ring128[33 + lane] = vb;
 
@@ -500,35 +502,38 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
                 lfB = movemask16(b0.lf, b1.lf, b2.lf, b3.lf);
                 const u32 ex = a0.ex | a1.ex | a2.ex | a3.ex | b0.ex | b1.ex | b2.ex | b3.ex;
                 liveA = dmA; liveB = dmB;
-                if (__any_sync(0xFFFFFFFFu, ex != 0) || carry.killed) {
+                if (__any_sync(0xFFFFFFFFu, ex != 0) || killed) {
                     acc_slow += lane == 0;
-                    const ExactOut oa = exact_sub(va, carry.killed, L.buf, L.n, L.base, T0, &st->stop, L.negate);
+                    const ExactOut oa = exact_sub(va, killed, L.buf, L.n, L.base, T0, &st->stop, L.negate);
                     const ExactOut ob = exact_sub(vb, oa.killed_out, L.buf, L.n, L.base, T0 + kSub, &st->stop, L.negate);
                     dmA = oa.dm; liveA = oa.live; lfA = oa.lfm;
                     dmB = ob.dm; liveB = ob.live; lfB = ob.lfm;
-                    carry.killed = ob.killed_out != 0;
+                    killed = ob.killed_out != 0;
                 }
             }
 
-            // ---- STOP: a line that is just "\n" (main.cu:185), or a 1-byte tail at the very end
+            // ---- what the byte before each lane's 16 bytes was: bit 0 line feed, bit 1 delimiter
+            u32 prevA, prevB;
             {
-                const u32 lastA = __shfl_sync(0xFFFFFFFFu, lfA >> 15, 31);
-                const u32 upA = __shfl_up_sync(0xFFFFFFFFu, lfA >> 15, 1), upB = __shfl_up_sync(0xFFFFFFFFu, lfB >> 15, 1);
-                const u32 prevA = lane == 0 ? (carry.last_is_lf ? 1u : 0u) : upA;
-                const u32 prevB = lane == 0 ? lastA : upB;
-                if (!L.negate) {
-                    const u32 startA = ((lfA << 1) | prevA) & 0xFFFFu, startB = ((lfB << 1) | prevB) & 0xFFFFu;
-                    const u32 blankA = lfA & startA, blankB = lfB & startB; // bit p: byte p starts a line
-                    if (blankA) atomicMin(&st->stop, L.base + T0 + lane * 16 + (__ffs(blankA) - 1));
-                    if (blankB) atomicMin(&st->stop, L.base + T0 + kSub + lane * 16 + (__ffs(blankB) - 1));
-                    if (L.last_piece && L.n - 1 >= T0 && L.n - 1 < T0 + kTile) {
-                        const u32 q = (u32)(L.n - 1 - T0); // position of the last byte in this tile
-                        const u32 own = q & 511, p = own & 15;
-                        const u32 starts = q < kSub ? startA : startB;
-                        if ((own >> 4) == lane && ((starts >> p) & 1)) atomicMin(&st->stop, L.base + L.n - 1);
-                    }
+                const u32 mineA = (lfA >> 15) | ((dmA >> 15) << 1), mineB = (lfB >> 15) | ((dmB >> 15) << 1);
+                const u32 upA = __shfl_up_sync(0xFFFFFFFFu, mineA, 1), upB = __shfl_up_sync(0xFFFFFFFFu, mineB, 1);
+                const u32 lastA = __shfl_sync(0xFFFFFFFFu, mineA, 31);
+                prevA = lane == 0 ? ((last_is_lf ? 1u : 0u) | (carry_prev == -1 ? 2u : 0u)) : upA;
+                prevB = lane == 0 ? lastA : upB;
+                last_is_lf = (__shfl_sync(0xFFFFFFFFu, mineB, 31) & 1u) != 0;
+            }
+            // ---- STOP: a line that is just "\n" (main.cu:185), or a 1-byte tail at the very end
+            if (!L.negate) {
+                const u32 startA = ((lfA << 1) | (prevA & 1u)) & 0xFFFFu, startB = ((lfB << 1) | (prevB & 1u)) & 0xFFFFu;
+                const u32 blankA = lfA & startA, blankB = lfB & startB; // bit p: byte p starts a line
+                if (blankA) atomicMin(&st->stop, L.base + T0 + lane * 16 + (__ffs(blankA) - 1));
+                if (blankB) atomicMin(&st->stop, L.base + T0 + kSub + lane * 16 + (__ffs(blankB) - 1));
+                if (L.last_piece && L.n - 1 >= T0 && L.n - 1 < T0 + kTile) {
+                    const u32 q = (u32)(L.n - 1 - T0); // position of the last byte in this tile
+                    const u32 own = q & 511, p = own & 15;
+                    const u32 starts = q < kSub ? startA : startB;
+                    if ((own >> 4) == lane && ((starts >> p) & 1)) atomicMin(&st->stop, L.base + L.n - 1);
                 }
-                carry.last_is_lf = __shfl_sync(0xFFFFFFFFu, lfB >> 15, 31) != 0;
             }
 
             // Roll-back launches only see flush points at or after range_lo.
@@ -539,7 +544,29 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
                 if (range_lo >= loB + 16) liveB = 0;
                 else if (range_lo > loB) liveB &= ~((1u << (u32)(range_lo - loB)) - 1);
             }
+
+            // ---- flush counts straight from the masks: a flush right after a delimiter is an empty word
+            const u32 afterA = ((dmA << 1) | (prevA >> 1)) & 0xFFFFu, afterB = ((dmB << 1) | (prevB >> 1)) & 0xFFFFu;
+            const u32 emA = liveA & afterA, emB = liveB & afterB;
             acc_flush += __popc(liveA) + __popc(liveB);
+            acc_empty += __popc(emA) + __popc(emB);
+            if (!seen_nonempty) { // this warp's first non-empty word, and the empty ones before it
+#pragma unroll
+                for (int sub = 0; sub < 2 && !seen_nonempty; sub++) {
+                    const u32 ne = sub ? (liveB & ~afterB) : (liveA & ~afterA), em = sub ? emB : emA;
+                    const u32 bn = __ballot_sync(0xFFFFFFFFu, ne != 0);
+                    u32 x = __popc(em);
+                    if (bn) {
+                        const u32 fl = __ffs(bn) - 1;
+                        const u32 pf = __shfl_sync(0xFFFFFFFFu, ne ? __ffs(ne) - 1 : 0, fl);
+                        if (lane == fl) x = __popc(em & ((1u << pf) - 1));
+                        if (lane > fl) x = 0;
+                        p0_rel = relT + sub * kSub + fl * 16 + pf;
+                        seen_nonempty = true;
+                    }
+                    my_empties_before += __reduce_add_sync(0xFFFFFFFFu, x);
+                }
+            }
 
             // ---- position-ordered list of every delimiter; one scan serves both sub-tiles
             const u32 cntA = __popc(dmA), cntB = __popc(dmB);
@@ -547,136 +574,114 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
             const u32 tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
             const u32 totA = tot & 0xFFFFu, totB = tot >> 16;
             const u32 exclA = (incl & 0xFFFFu) - cntA, exclB = (incl >> 16) - cntB;
-            const u32 relT = (u32)(T0 - cta_base);
 
             // The list holds at most kDlCap entries: a tile dense with delimiters is done one sub-tile
             // at a time.  `first_prev` is the position (tile relative, negative if it lies before the
             // tile) of the delimiter that precedes list entry 0.
-            long long cr = carry.last_delim - (long long)T0; // <= -1
-            int first_prev = cr < -4096 ? -4096 : (int)cr;
+            int first_prev = carry_prev;
             const bool dense = totA + totB > (u32)kDlCap;
             for (int ph = 0; ph < (dense ? 2 : 1); ph++) {
                 if (!dense || ph == 0) {
-                    u32 idx = exclA, m = dmA;
+                    u32 m = dmA;
+                    unsigned short *o = dl + exclA;
+                    const u32 basepos = lane * 16;
+#pragma unroll
+                    for (int i = 0; i < 4; i++) { // most lanes hold at most 4 delimiters
+                        const u32 p = __ffs(m) - 1;
+                        if (m) o[i] = (unsigned short)((basepos + p) | (((liveA >> p) & 1u) << 15));
+                        m &= m - 1;
+                    }
+                    o += 4;
                     while (m) {
                         const u32 p = __ffs(m) - 1; m &= m - 1;
-                        dl[idx++] = (unsigned short)((lane * 16 + p) | (((liveA >> p) & 1u) << 15));
+                        *o++ = (unsigned short)((basepos + p) | (((liveA >> p) & 1u) << 15));
                     }
                 }
                 if (!dense || ph == 1) {
-                    u32 idx = (dense ? 0u : totA) + exclB, m = dmB;
+                    u32 m = dmB;
+                    unsigned short *o = dl + (dense ? 0u : totA) + exclB;
+                    const u32 basepos = kSub + lane * 16;
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const u32 p = __ffs(m) - 1;
+                        if (m) o[i] = (unsigned short)((basepos + p) | (((liveB >> p) & 1u) << 15));
+                        m &= m - 1;
+                    }
+                    o += 4;
                     while (m) {
                         const u32 p = __ffs(m) - 1; m &= m - 1;
-                        dl[idx++] = (unsigned short)((kSub + lane * 16 + p) | (((liveB >> p) & 1u) << 15));
+                        *o++ = (unsigned short)((basepos + p) | (((liveB >> p) & 1u) << 15));
                     }
                 }
                 __syncwarp();
                 const u32 total = dense ? (ph ? totB : totA) : totA + totB;
-                // ---- one word per lane
+
+                // ---- one word per lane; straight-line code, the rare cases are deferred
                 for (u32 k0 = 0; k0 < total; k0 += 32) {
                     const u32 k = k0 + lane;
                     const u32 d = k < total ? (u32)dl[k] : 0u;
                     const u32 d_up = __shfl_up_sync(0xFFFFFFFFu, d, 1);
+                    const int before = k0 ? (int)(dl[k0 - 1] & 0x3FFu) : first_prev; // same for every lane
                     const int e = (int)(d & 0x3FFu);
-                    int prev = (int)(d_up & 0x3FFu);
-                    if (lane == 0) prev = k0 ? (int)(dl[k0 - 1] & 0x3FFu) : first_prev;
+                    const int prev = lane ? (int)(d_up & 0x3FFu) : before;
                     const int len = e - prev - 1;
-                    const bool flushes = (d >> 15) != 0;
-                    const bool nonempty = flushes && len > 0;
-                    if (flushes && len == 0) acc_empty++;
+                    const bool word = (d >> 15) && len > 0;       // a flush of a non-empty word
+                    const bool is_short = word && len <= 8;
+                    const int klen = is_short ? len : 1;          // keeps the reads below in bounds
 
-                    if (!seen_nonempty) { // still looking for this warp's first non-empty word
-                        const u32 bn = __ballot_sync(0xFFFFFFFFu, nonempty);
-                        const u32 be = __ballot_sync(0xFFFFFFFFu, flushes && len == 0);
-                        if (bn) {
-                            const u32 fl = __ffs(bn) - 1;
-                            my_empties_before += __popc(be & ((1u << fl) - 1));
-                            my_p0 = L.base + T0 + (u64)__shfl_sync(0xFFFFFFFFu, e, fl);
-                            seen_nonempty = true;
-                        } else my_empties_before += __popc(be);
+                    // key = the word's bytes, from the warp's shared-memory copy of the tile
+                    const u32 idx = (u32)(16 + e - klen);          // >= 8: reaches into the previous tile's tail
+                    const u32 *r = ring32 + (idx >> 2);
+                    const u32 w0 = r[0], w1 = r[1], w2 = r[2];
+                    const u32 sh = (idx & 3) * 8;
+                    u32 klo = __funnelshift_r(w0, w1, sh), khi = __funnelshift_r(w1, w2, sh);
+                    const u32 nb8 = 8 * (u32)klen;
+                    klo &= nb8 >= 32 ? 0xFFFFFFFFu : ((1u << nb8) - 1);
+                    khi &= nb8 > 32 ? (0xFFFFFFFFu >> (64 - nb8)) : 0u;
+
+                    // single-probe shared-memory table: hit, claim an empty slot, or defer
+                    const u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);
+                    uint4 ent = tab[slot];
+                    bool hit = is_short && ent.x == klo && ent.y == khi;
+                    if (is_short && !hit && (ent.x | ent.y) == 0) { // only while the table fills up
+                        const u64 key = (u64)klo | ((u64)khi << 32);
+                        const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[slot]), 0ull, key);
+                        hit = old == 0 || old == key;
+                        ent.w = 0xFFFFFFFFu;
                     }
-
-                    const bool is_long = nonempty && len > 8;
-                    bool spill = false;
-                    u32 klo = 0, khi = 0;
                     const u32 rel = relT + (u32)e;
-                    if (nonempty && !is_long) {
-                        // ---- key = the word's bytes, from the warp's shared-memory copy of the tile
-                        const u32 idx = (u32)(16 + e - len); // >= 8: reaches into the previous tile's tail
-                        const u32 *r = ring32 + (idx >> 2);
-                        const u32 w0 = r[0], w1 = r[1], w2 = r[2];
-                        const u32 sh = (idx & 3) * 8;
-                        klo = __funnelshift_r(w0, w1, sh);
-                        khi = __funnelshift_r(w1, w2, sh);
-                        const u64 m = ~0ull >> (64 - 8 * len);
-                        klo &= (u32)m; khi &= (u32)(m >> 32);
+                    u32 *cell = reinterpret_cast<u32 *>(&tab[slot]);
+                    if (hit) atomicAdd(cell + 2, delta32);
+                    if (hit && rel < ent.w) atomicMin(cell + 3, rel);
 
-                        // ---- single-probe shared-memory table: hit, claim an empty slot, or spill
-                        const u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);
-                        uint4 ent = tab[slot];
-                        bool hit = ent.x == klo && ent.y == khi;
-                        if (!hit && (ent.x | ent.y) == 0) {
-                            const u64 key = (u64)klo | ((u64)khi << 32);
-                            const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[slot]), 0ull, key);
-                            hit = old == 0 || old == key;
-                            ent.w = 0xFFFFFFFFu;
-                        }
-                        if (hit) {
-                            u32 *cell = reinterpret_cast<u32 *>(&tab[slot]);
-                            atomicAdd(cell + 2, delta32);
-                            if (rel < ent.w) atomicMin(cell + 3, rel);
-                        }
-                        spill = !hit;
-                    }
-
-                    // ---- words the table has no room for, and words of 9+ bytes, are queued
-                    const u32 bs = __ballot_sync(0xFFFFFFFFu, spill);
-                    if (bs) {
-                        if (spill) {
-                            const u32 qi = sq_count + __popc(bs & ((1u << lane) - 1));
-                            sq_key[qi] = (u64)klo | ((u64)khi << 32);
-                            sq_rel[qi] = rel;
-                        }
-                        sq_count += __popc(bs);
-                        n_spill += spill;
+                    const bool defer = word && !hit;
+                    const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
+                    if (bq) {
+                        if (defer) dq[q_count + __popc(bq & lt_mask)] = make_uint2(rel, (u32)len);
+                        q_count += __popc(bq);
+                        n_long += defer && !is_short;
+                        n_spill += defer && is_short;
                         __syncwarp();
-                        if (sq_count >= 32) drain_spill(32);
-                    }
-                    const u32 bl = __ballot_sync(0xFFFFFFFFu, is_long);
-                    if (bl) {
-                        if (is_long) {
-                            const u32 qi = lq_count + __popc(bl & ((1u << lane) - 1));
-                            // entry 0's word may start far back: its true start is the carried delimiter + 1
-                            const long long start = (k == 0 && first_prev < 0) ? carry.last_delim + 1
-                                                                               : (long long)T0 + prev + 1;
-                            const long long wl = (long long)T0 + e - start;
-                            lq_start[qi] = (u64)start;
-                            if (wl > 0x7FFFFFFFll) { atomicOr(&st->err, kErrWordTooLong); lq_len[qi] = 9; }
-                            else lq_len[qi] = (u32)wl;
-                            n_long++;
+                        if (q_count >= 32) {
+                            n_made += drain_deferred(dq, q_count, 32, &L, &T, cta_base);
+                            q_count -= 32;
                         }
-                        lq_count += __popc(bl);
-                        __syncwarp();
-                        if (lq_count >= 32) drain_long(32);
                     }
                 }
-                if (total > 0) {
-                    first_prev = (int)(dl[total - 1] & 0x3FFu);
-                    carry.last_delim = (long long)T0 + first_prev;
-                }
+                if (total > 0) first_prev = (int)(dl[total - 1] & 0x3FFu);
                 __syncwarp();
             }
-            __syncwarp();
+            // the next tile sees this tile's last delimiter at a negative position
+            carry_prev = first_prev - kTile < -(1 << 30) ? -(1 << 30) : first_prev - kTile;
             if (lane == 31) ring128[0] = vb; // the next tile's words may start in this tile's last bytes
             __syncwarp();
         }
-        if (sq_count > 0) drain_spill(sq_count);
-        if (lq_count > 0) drain_long(lq_count);
+        if (q_count > 0) n_made += drain_deferred(dq, q_count, q_count, &L, &T, cta_base);
     }
 
     // ---- per-warp results
     const u64 w_flush = warp_sum64(acc_flush), w_empty = warp_sum64(acc_empty);
-    const u32 w_lnew = __reduce_add_sync(0xFFFFFFFFu, n_lnew);
+    const u32 w_lnew = __reduce_add_sync(0xFFFFFFFFu, n_made >> 16);
     const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, n_long), w_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
     if (lane == 0) {
         if (w_flush) atomicAdd(&st->n_flush, L.negate ? (u64)(-(long long)w_flush) : w_flush);
@@ -687,7 +692,7 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
             if (w_spill) atomicAdd(&st->n_spill, (u64)w_spill);
             if (acc_slow) atomicAdd(&st->n_slow_tiles, (u64)acc_slow);
             if (L.ws != nullptr && gwarp < L.n_ws) {
-                L.ws[gwarp].p0 = my_p0;
+                L.ws[gwarp].p0 = (seen_nonempty && t0 < t1) ? L.base + cta_base + p0_rel : kNone;
                 L.ws[gwarp].empties_before = my_empties_before;
                 L.ws[gwarp].empties_total = w_empty;
             }
@@ -696,6 +701,8 @@ __global__ void __launch_bounds__(kThreads, 1) count_kernel(const Launch L, cons
 
     // ---- flush the CTA's table into the global one
     __syncthreads();
+    u32 n_snew = n_made & 0xFFFFu;
+    const u64 delta_sign = L.negate ? ~0ull : 0ull; (void)delta_sign;
     for (u32 i = tid; i < kSmemEntries; i += kThreads) {
         const uint4 ent = tab[i];
         if ((ent.x | ent.y) != 0 && ent.z != 0) {
