@@ -100,11 +100,11 @@ def workload_params(name, n_gpus):
     from tools.corpus import CONFIGS
     if name == "config2":
         per_gpu = CONFIGS[2]["bytes"]  # 1e9 B per GPU (weak scaling for N > 1)
-        return dict(config=2, total=per_gpu * n_gpus, per_gpu=per_gpu, s_log2=18, l_log2=16,
+        return dict(config=2, total=per_gpu * n_gpus, per_gpu=per_gpu, s_log2=18, l_log2=12,
                     label="config2: Zipf(1.1) English-like text, 50k-word vocabulary, 1e9 B per GPU")
     if name == "config3":
         total = CONFIGS[3]["bytes"]
-        return dict(config=3, total=total, per_gpu=total // n_gpus, s_log2=21, l_log2=21,
+        return dict(config=3, total=total, per_gpu=total // n_gpus, s_log2=22, l_log2=14,
                     label="config3: Zipf(1.1) text, 1M-word vocabulary, 1.6e10 B over all GPUs")
     raise SystemExit("unknown workload " + name)
 
@@ -263,7 +263,7 @@ def main():
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_val = all_bytes / te.item() / 1e9
-    d2h = 3 * 8 * ((1 << wp["s_log2"]) + (1 << wp["l_log2"])) + 512
+    d2h = 8 * (4 * (1 << wp["s_log2"]) + 3 * (1 << wp["l_log2"])) + 512
 
     if rank != 0:
         return
@@ -274,6 +274,8 @@ def main():
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
         "config": {"workload": wp["label"], "bytes_per_gpu": nbytes, "words_per_gpu": words,
+                   "distinct_words": res.stats["n_distinct"], "deferred_1to8B_words": res.stats["n_spilled"],
+                   "words_9B_plus": res.stats["n_long_words"],
                    "l2": "input (1e9 B) is larger than the 126 MB L2, every step re-reads it from HBM",
                    "step": "wc_reset (table memset) + tokenize/count kernel + roll-back/summary kernel",
                    "vocab_seed": corpus.vocab_seed, "text_seed": corpus.text_seed},

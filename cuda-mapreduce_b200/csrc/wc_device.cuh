@@ -22,31 +22,32 @@ constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 
 constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = 16;                 // warps per CTA
 constexpr int kThreads = kWarps * 32;
-constexpr u32 kSmemEntries = 11904;        // 16-byte entries of the per-CTA table (186 KiB)
-constexpr int kRingBytes = 1072;           // per warp: 16 B tail of the previous tile + the tile + slack
+constexpr u32 kSmemEntries = 9792;         // 16-byte entries of the per-CTA table (153 KiB)
+constexpr int kBufBytes = 1072;            // one tile buffer: 16 B tail of the previous tile + tile + slack
+constexpr int kRingBytes = 2 * kBufBytes;  // per warp: two buffers, the next tile lands by cp.async
 constexpr int kDlCap = 512;                // per warp: delimiter list entries
 constexpr int kDlBytes = kDlCap * 2;
-constexpr int kQueue = 64;                 // per warp: deferred words (8-byte records)
+constexpr int kQueue = 64;                 // per warp: deferred words (16-byte key + 8-byte record)
 constexpr u64 kNone = ~0ull;
 
-constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kQueue * 8;
+constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kQueue * 24;
 constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16;
 constexpr size_t kSmemTotal = kSmemTableBytes + (size_t)kWarps * kWarpSmemBytes;
 static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
 static_assert(kSmemTotal <= 232448 - 64, "more shared memory than an sm_100 CTA can have");
 
-enum : u32 { kErrShortFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u };
+enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u };
 
 // Device-resident job state (one per engine).
 struct Status {
     u64 n_flush;      // words emitted, empty ones included (two's complement adds for roll-back)
     u64 n_empty;
     u64 stop;         // min offset at which the reference stops reading (main.cu:185); kNone if none
-    u64 s_entries;    // claimed slots, short table
-    u64 l_entries;    // claimed slots, long table
-    u64 n_long;       // words > 8 bytes
-    u64 n_spill;      // short words that went straight to the global table
-    u64 n_slow_tiles; // tiles that took the CR / NUL line-state path
+    u64 w_entries;    // claimed slots, word table (1..16 bytes)
+    u64 x_entries;    // claimed slots, long table (17+ bytes)
+    u64 n_long;       // words of 9+ bytes (they bypass the shared-memory table)
+    u64 n_spill;      // words of 1..8 bytes the shared-memory table had no room for
+    u64 n_slow_tiles; // tiles that took the exact line-state path (control bytes)
     u64 arena_used;   // 8-byte units handed out (unit 0 is never used)
     u64 p0;           // offset that flushed the first non-empty word
     u64 lost_empty;   // empty words before p0 (main.cu:81,103: lost)
@@ -55,12 +56,13 @@ struct Status {
 };
 
 struct Tables {
-    // words of 1..8 bytes: the key is the word itself, zero padded (exact by value)
-    u64 *s_keys, *s_counts, *s_finv; // finv = ~first_offset, so 0 == unset and atomicMax keeps the min
-    u32 s_log2;
-    // words of 9+ bytes: slot = (24-bit hash tag << 40) | arena unit index; bytes compared in the arena
-    u64 *l_refs, *l_counts, *l_finv;
-    u32 l_log2;
+    // words of 1..16 bytes: the key is the word itself, zero padded to 16 (exact by value)
+    ulonglong2 *w_keys;
+    u64 *w_counts, *w_finv; // finv = ~first_offset, so 0 == unset and atomicMax keeps the min
+    u32 w_log2;
+    // words of 17+ bytes: slot = (24-bit hash tag << 40) | arena unit index; bytes compared in the arena
+    u64 *x_refs, *x_counts, *x_finv;
+    u32 x_log2;
     u64 *arena;       // unit[i] = length, unit[i+1..] = bytes, zero padded to 8
     u64 arena_units;
     Status *st;
@@ -155,29 +157,56 @@ __device__ __forceinline__ u64 warp_sum64(u64 v) {
     return v;
 }
 
-// ------------------------------------------------------- global short table
+// ------------------------------------------------------- global word table (1..16 bytes)
 
-// Adds `delta` occurrences of a 1..8-byte word to the global table; returns 1 if it claimed a new slot.
-__device__ __forceinline__ u32 gs_insert(const Tables &T, u64 key, u64 delta, u64 first_abs) {
-    const u64 mask = (1ull << T.s_log2) - 1;
-    u64 slot = mix64(key) >> (64 - T.s_log2);
+__host__ __device__ __forceinline__ u32 hash_key128(u32 a, u32 b, u32 c, u32 d) {
+    u32 h = a * 0x9E3779B1u;
+    h ^= b * 0x85EBCA77u;
+    h ^= c * 0xC2B2AE3Du;
+    h ^= d * 0x27D4EB2Fu;
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du;
+    h ^= h >> 13;
+    h *= 0x297A2D39u;
+    h ^= h >> 16;
+    return h;
+}
+
+__device__ __forceinline__ ulonglong2 cas128(ulonglong2 *addr, ulonglong2 cmp, ulonglong2 val) {
+    ulonglong2 old;
+    asm volatile("{\n\t.reg .b128 c, v, o;\n\t"
+                 "mov.b128 c, {%3, %4};\n\t"
+                 "mov.b128 v, {%5, %6};\n\t"
+                 "atom.global.cas.b128 o, [%2], c, v;\n\t"
+                 "mov.b128 {%0, %1}, o;\n\t}"
+                 : "=l"(old.x), "=l"(old.y)
+                 : "l"(addr), "l"(cmp.x), "l"(cmp.y), "l"(val.x), "l"(val.y)
+                 : "memory");
+    return old;
+}
+
+// Adds `delta` occurrences of a word of 1..16 bytes (k0 = bytes 0..7, k1 = bytes 8..15, zero padded)
+// to the global table; returns 1 if it claimed a new slot.
+__device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u64 delta, u64 first_abs) {
+    const u32 mask = (u32)((1ull << T.w_log2) - 1);
+    u32 slot = hash_key128((u32)k0, (u32)(k0 >> 32), (u32)k1, (u32)(k1 >> 32)) >> (32 - T.w_log2);
     u32 is_new = 0;
     for (u32 probes = 0;; ++probes) {
-        u64 k = __ldcg(&T.s_keys[slot]);
-        if (k == 0) {
-            k = atomicCAS(&T.s_keys[slot], 0ull, key);
-            if (k == 0) { is_new = 1; k = key; }
+        ulonglong2 k = __ldcg(&T.w_keys[slot]);
+        if (k.x == 0) { // a used slot never has k.x == 0: a word's first byte is not 0x00
+            k = cas128(&T.w_keys[slot], make_ulonglong2(0, 0), make_ulonglong2(k0, k1));
+            if (k.x == 0) { is_new = 1; k.x = k0; k.y = k1; }
         }
-        if (k == key) break;
+        if (k.x == k0 && k.y == k1) break;
         slot = (slot + 1) & mask;
-        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrShortFull); return 0; }
+        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrWordFull); return 0; }
     }
-    atomicAdd(&T.s_counts[slot], delta); // both fire-and-forget (RED)
-    atomicMax(&T.s_finv[slot], ~first_abs);
+    atomicAdd(&T.w_counts[slot], delta); // both fire-and-forget (RED)
+    atomicMax(&T.w_finv[slot], ~first_abs);
     return is_new;
 }
 
-// -------------------------------------------------------- global long table
+// -------------------------------------------------------- global long table (17+ bytes)
 
 __device__ __forceinline__ u64 long_hash(const uint8_t *buf, u64 start, u64 len) {
     u64 h = 0x9E3779B97F4A7C15ull ^ (len * 0xFF51AFD7ED558CCDull);
@@ -206,18 +235,19 @@ __device__ __forceinline__ bool long_equal(const Tables &T, u64 unit, const uint
     return true;
 }
 
-// A word of 9+ bytes at buf[start, start+len).  Never waits on another thread: a new word is
+// A word of 17+ bytes at buf[start, start+len).  Never waits on another thread: a new word is
 // first written to the arena, then published with one CAS of the slot word.  Returns 1 if new.
-__device__ __noinline__ u32 long_insert(const Tables T, const uint8_t *buf, u64 start, u64 len, u64 delta,
+__device__ __noinline__ u32 long_insert(const Tables *Tp, const uint8_t *buf, u64 start, u64 len, u64 delta,
                                         u64 first_abs) {
+    const Tables &T = *Tp;
     const u64 h = long_hash(buf, start, len);
-    const u64 mask = (1ull << T.l_log2) - 1;
+    const u64 mask = (1ull << T.x_log2) - 1;
     const u64 tag = h >> 40;
     u64 slot = h & mask;
     u64 my_ref = 0;
     u32 is_new = 0;
     for (u32 probes = 0;; ++probes) {
-        u64 r = __ldcg(&T.l_refs[slot]);
+        u64 r = __ldcg(&T.x_refs[slot]);
         if (r == 0) {
             if (my_ref == 0) {
                 u64 units = 1 + ((len + 7) >> 3);
@@ -230,15 +260,15 @@ __device__ __noinline__ u32 long_insert(const Tables T, const uint8_t *buf, u64 
                 __threadfence();
                 my_ref = (tag << 40) | idx;
             }
-            r = atomicCAS(&T.l_refs[slot], 0ull, my_ref);
+            r = atomicCAS(&T.x_refs[slot], 0ull, my_ref);
             if (r == 0) { is_new = 1; break; }
         }
         if ((r >> 40) == tag && long_equal(T, r & ((1ull << 40) - 1), buf, start, len)) break;
         slot = (slot + 1) & mask;
         if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrLongFull); return 0; }
     }
-    atomicAdd(&T.l_counts[slot], delta);
-    atomicMax(&T.l_finv[slot], ~first_abs);
+    atomicAdd(&T.x_counts[slot], delta);
+    atomicMax(&T.x_finv[slot], ~first_abs);
     return is_new;
 }
 
@@ -359,30 +389,50 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
     return o;
 }
 
-// Deferred words: short words the CTA's table had no room for, and every word of 9+ bytes.  A
-// record is (end offset relative to the CTA's range, length).  They are inserted into the global
-// tables 32 at a time, so that every lane has its global-memory accesses in flight at once instead
-// of the whole warp waiting on two or three.  Returns new short slots | new long slots << 16.
-__device__ __noinline__ u32 drain_deferred(uint2 *q, u32 count, u32 take, const Launch *Lp, const Tables *Tp,
-                                           u64 cta_base) {
+// Deferred words: words of 1..8 bytes the CTA's table had no room for, and every word of 9+ bytes.
+// A record is the word's first 16 bytes plus (end offset relative to the CTA's range, length).
+// They are inserted into the global tables 32 at a time, so that every lane has its global-memory
+// accesses in flight at once instead of the whole warp waiting on two or three.
+// Returns new word-table slots | new long-table slots << 16.
+__device__ __noinline__ u32 drain_deferred(uint4 *qk, uint2 *qm, u32 count, u32 take, const Launch *Lp,
+                                           const Tables *Tp, u64 cta_base) {
     const u32 lane = lane_id();
     u32 made = 0;
     if (lane < take) {
-        const uint2 rec = q[lane];
-        const u64 end = cta_base + rec.x;      // buffer-relative offset of the delimiter
-        const u64 start = end - rec.y;
+        const uint4 k = qk[lane];
+        const uint2 rec = qm[lane];
+        const u64 end = cta_base + rec.x; // buffer-relative offset of the delimiter
         const u64 delta = Lp->negate ? ~0ull : 1ull;
-        if (rec.y <= 8) made = gs_insert(*Tp, load8_unaligned(Lp->buf, start, rec.y), delta, Lp->base + end);
-        else made = long_insert(*Tp, Lp->buf, start, rec.y, delta, Lp->base + end) << 16;
+        if (rec.y <= 16)
+            made = word_insert(*Tp, (u64)k.x | ((u64)k.y << 32), (u64)k.z | ((u64)k.w << 32), delta, Lp->base + end);
+        else
+            made = long_insert(Tp, Lp->buf, end - rec.y, rec.y, delta, Lp->base + end) << 16;
     }
     __syncwarp();
-    uint2 mv = make_uint2(0, 0);
+    uint4 mk = make_uint4(0, 0, 0, 0); uint2 mm = make_uint2(0, 0);
     const bool keep = lane + take < count;
-    if (keep) mv = q[lane + take];
+    if (keep) { mk = qk[lane + take]; mm = qm[lane + take]; }
     __syncwarp();
-    if (keep) q[lane] = mv;
+    if (keep) { qk[lane] = mk; qm[lane] = mm; }
     __syncwarp();
     return made;
+}
+
+__device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+
+// One lane's two 16-byte pieces of tile `tile` into its buffer: asynchronous copies when the
+// bytes are all inside the input, a padded synchronous load at the very end of it.
+__device__ __forceinline__ void fetch_tile(const Launch &L, u64 tile, unsigned char *buf, u32 lane) {
+    const u64 offA = tile * kTile + lane * 16, offB = offA + kSub;
+    unsigned char *dA = buf + 16 + lane * 16, *dB = dA + kSub;
+    if (offB + 16 <= L.n) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(dA)), "l"(L.buf + offA) : "memory");
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(dB)), "l"(L.buf + offB) : "memory");
+    } else {
+        *reinterpret_cast<uint4 *>(dA) = load16(L.buf, L.n, offA);
+        *reinterpret_cast<uint4 *>(dB) = load16(L.buf, L.n, offB);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
 extern __shared__ __align__(16) unsigned char wc_smem[];
@@ -439,12 +489,11 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     for (u32 i = tid; i < kSmemEntries; i += kThreads) tab[i] = make_uint4(0, 0, 0, 0xFFFFFFFFu);
     __syncthreads();
 
-    // per-warp shared memory: [prev tail 16 B | tile 1024 B | slack] [delimiter list] [deferred queue]
+    // per-warp shared memory: [two tile buffers] [delimiter list] [deferred keys] [deferred records]
     unsigned char *wbase = warp_all + warp * kWarpSmemBytes;
-    uint4 *ring128 = reinterpret_cast<uint4 *>(wbase);
-    const u32 *ring32 = reinterpret_cast<const u32 *>(wbase);
     unsigned short *dl = reinterpret_cast<unsigned short *>(wbase + kRingBytes);
-    uint2 *dq = reinterpret_cast<uint2 *>(wbase + kRingBytes + kDlBytes);
+    uint4 *dqk = reinterpret_cast<uint4 *>(wbase + kRingBytes + kDlBytes);
+    uint2 *dqm = reinterpret_cast<uint2 *>(wbase + kRingBytes + kDlBytes + kQueue * 16);
 
     const u32 tiles_total = (u32)((L.n + kTile - 1) / kTile);
     const u32 gwarp = blockIdx.x * kWarps + warp;
@@ -457,7 +506,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     }
     const u32 lt_mask = (1u << lane) - 1;
 
-    u32 n_made = 0;                                  // new global slots: short | long << 16
+    u32 n_made = 0;                                  // new global slots: word table | long table << 16
     u32 n_long = 0, n_spill = 0;
     u32 acc_flush = 0, acc_empty = 0, acc_slow = 0;  // per lane; a warp's range is < 4 GiB
     u32 q_count = 0;
@@ -474,20 +523,25 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             const long long cr = c.last_delim - (long long)t0 * kTile;
             carry_prev = cr < -(1ll << 30) ? -(1 << 30) : (int)cr;
             killed = c.killed; last_is_lf = c.last_is_lf;
-            if (lane == 0) ring128[0] = load16(L.buf, L.n, (u64)t0 * kTile - 16);
+            // the bytes just before the range, where a word ending in the first tile may start
+            if (lane == 0)
+                *reinterpret_cast<uint4 *>(wbase + (t0 & 1) * kBufBytes) = load16(L.buf, L.n, (u64)t0 * kTile - 16);
         }
-        uint4 na = load16(L.buf, L.n, (u64)t0 * kTile + lane * 16);
-        uint4 nb = load16(L.buf, L.n, (u64)t0 * kTile + kSub + lane * 16);
+        fetch_tile(L, t0, wbase + (t0 & 1) * kBufBytes, lane);
         for (u32 t = t0; t < t1; ++t) {
-            const uint4 va = na, vb = nb;
-            if (t + 1 < t1) {
-                na = load16(L.buf, L.n, (u64)(t + 1) * kTile + lane * 16);
-                nb = load16(L.buf, L.n, (u64)(t + 1) * kTile + kSub + lane * 16);
+            unsigned char *buf = wbase + (t & 1) * kBufBytes;
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            if (t + 1 < t1) { // next tile into the other buffer, with this tile's last 16 bytes in front of it
+                unsigned char *nbuf = wbase + ((t + 1) & 1) * kBufBytes;
+                if (lane == 31) *reinterpret_cast<uint4 *>(nbuf) = *reinterpret_cast<const uint4 *>(buf + kTile);
+                fetch_tile(L, t + 1, nbuf, lane);
             }
+            const u32 *ring32 = reinterpret_cast<const u32 *>(buf);
+            const uint4 va = *reinterpret_cast<const uint4 *>(buf + 16 + lane * 16);
+            const uint4 vb = *reinterpret_cast<const uint4 *>(buf + 16 + kSub + lane * 16);
             const u64 T0 = (u64)t * kTile;          // buffer-relative offset of this tile
             const u32 relT = (u32)(T0 - cta_base);
-            ring128[1 + lane] = va;
-            ring128[33 + lane] = vb;
 
             // ---- classify 2 x 16 bytes
             u32 dmA, dmB, lfA, lfB, liveA, liveB;
@@ -627,17 +681,17 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const int len = e - prev - 1;
                     const bool word = (d >> 15) && len > 0;       // a flush of a non-empty word
                     const bool is_short = word && len <= 8;
-                    const int klen = is_short ? len : 1;          // keeps the reads below in bounds
+                    const int rlen = len > 16 ? 16 : (len < 1 ? 1 : len); // bytes looked at (keeps reads in bounds)
 
-                    // key = the word's bytes, from the warp's shared-memory copy of the tile
-                    const u32 idx = (u32)(16 + e - klen);          // >= 8: reaches into the previous tile's tail
+                    // key = the word's first 8 bytes, from the warp's shared-memory copy of the tile
+                    const u32 idx = (u32)(16 + e - rlen);          // >= 0: reaches into the previous tile's tail
                     const u32 *r = ring32 + (idx >> 2);
                     const u32 w0 = r[0], w1 = r[1], w2 = r[2];
                     const u32 sh = (idx & 3) * 8;
                     u32 klo = __funnelshift_r(w0, w1, sh), khi = __funnelshift_r(w1, w2, sh);
-                    const u32 nb8 = 8 * (u32)klen;
+                    const u32 nb8 = 8 * (u32)rlen;
                     klo &= nb8 >= 32 ? 0xFFFFFFFFu : ((1u << nb8) - 1);
-                    khi &= nb8 > 32 ? (0xFFFFFFFFu >> (64 - nb8)) : 0u;
+                    khi &= nb8 >= 64 ? 0xFFFFFFFFu : (nb8 > 32 ? ((1u << (nb8 - 32)) - 1) : 0u);
 
                     // single-probe shared-memory table: hit, claim an empty slot, or defer
                     const u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);
@@ -657,13 +711,25 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const bool defer = word && !hit;
                     const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
                     if (bq) {
-                        if (defer) dq[q_count + __popc(bq & lt_mask)] = make_uint2(rel, (u32)len);
+                        if (defer) {
+                            u32 k1lo = 0, k1hi = 0;
+                            if (len > 8) { // bytes 8..15 of a longer word
+                                const u32 w3 = r[3], w4 = r[4];
+                                k1lo = __funnelshift_r(w2, w3, sh); k1hi = __funnelshift_r(w3, w4, sh);
+                                const u32 mb = nb8 - 64; // 8..64 bits
+                                k1lo &= mb >= 32 ? 0xFFFFFFFFu : ((1u << mb) - 1);
+                                k1hi &= mb >= 64 ? 0xFFFFFFFFu : (mb > 32 ? ((1u << (mb - 32)) - 1) : 0u);
+                            }
+                            const u32 qi = q_count + __popc(bq & lt_mask);
+                            dqk[qi] = make_uint4(klo, khi, k1lo, k1hi);
+                            dqm[qi] = make_uint2(rel, (u32)len);
+                            n_long += !is_short;
+                            n_spill += is_short;
+                        }
                         q_count += __popc(bq);
-                        n_long += defer && !is_short;
-                        n_spill += defer && is_short;
                         __syncwarp();
                         if (q_count >= 32) {
-                            n_made += drain_deferred(dq, q_count, 32, &L, &T, cta_base);
+                            n_made += drain_deferred(dqk, dqm, q_count, 32, &L, &T, cta_base);
                             q_count -= 32;
                         }
                     }
@@ -673,20 +739,18 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             }
             // the next tile sees this tile's last delimiter at a negative position
             carry_prev = first_prev - kTile < -(1 << 30) ? -(1 << 30) : first_prev - kTile;
-            if (lane == 31) ring128[0] = vb; // the next tile's words may start in this tile's last bytes
-            __syncwarp();
         }
-        if (q_count > 0) n_made += drain_deferred(dq, q_count, q_count, &L, &T, cta_base);
+        if (q_count > 0) n_made += drain_deferred(dqk, dqm, q_count, q_count, &L, &T, cta_base);
     }
 
     // ---- per-warp results
     const u64 w_flush = warp_sum64(acc_flush), w_empty = warp_sum64(acc_empty);
-    const u32 w_lnew = __reduce_add_sync(0xFFFFFFFFu, n_made >> 16);
+    const u32 w_xnew = __reduce_add_sync(0xFFFFFFFFu, n_made >> 16);
     const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, n_long), w_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
     if (lane == 0) {
         if (w_flush) atomicAdd(&st->n_flush, L.negate ? (u64)(-(long long)w_flush) : w_flush);
         if (w_empty) atomicAdd(&st->n_empty, L.negate ? (u64)(-(long long)w_empty) : w_empty);
-        if (w_lnew) atomicAdd(&st->l_entries, (u64)w_lnew);
+        if (w_xnew) atomicAdd(&st->x_entries, (u64)w_xnew);
         if (!L.negate) {
             if (w_long) atomicAdd(&st->n_long, (u64)w_long);
             if (w_spill) atomicAdd(&st->n_spill, (u64)w_spill);
@@ -701,48 +765,16 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
 
     // ---- flush the CTA's table into the global one
     __syncthreads();
-    u32 n_snew = n_made & 0xFFFFu;
-    const u64 delta_sign = L.negate ? ~0ull : 0ull; (void)delta_sign;
+    u32 n_wnew = n_made & 0xFFFFu;
     for (u32 i = tid; i < kSmemEntries; i += kThreads) {
         const uint4 ent = tab[i];
         if ((ent.x | ent.y) != 0 && ent.z != 0) {
             const u64 key = (u64)ent.x | ((u64)ent.y << 32);
-            n_snew += gs_insert(T, key, (u64)(long long)(int)ent.z, L.base + cta_base + ent.w);
+            n_wnew += word_insert(T, key, 0ull, (u64)(long long)(int)ent.z, L.base + cta_base + ent.w);
         }
     }
-    const u32 w_snew = __reduce_add_sync(0xFFFFFFFFu, n_snew);
-    if (lane == 0 && w_snew) atomicAdd(&st->s_entries, (u64)w_snew);
-}
-
-// ------------------------------------------------------------ table growth
-
-__global__ void rehash_short_kernel(const u64 *keys, const u64 *counts, const u64 *finv, u64 n_old, Tables T) {
-    for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n_old; i += (u64)gridDim.x * blockDim.x) {
-        const u64 k = keys[i];
-        if (k == 0) continue;
-        gs_insert(T, k, counts[i], ~finv[i]);
-    }
-}
-
-__global__ void rehash_long_kernel(const u64 *refs, const u64 *counts, const u64 *finv, u64 n_old, Tables T) {
-    const u64 mask = (1ull << T.l_log2) - 1;
-    for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n_old; i += (u64)gridDim.x * blockDim.x) {
-        const u64 r = refs[i];
-        if (r == 0) continue;
-        const u64 unit = r & ((1ull << 40) - 1);
-        const u64 len = T.arena[unit];
-        // same hash as long_hash(), over the arena copy (8-byte aligned, zero padded)
-        u64 h = 0x9E3779B97F4A7C15ull ^ (len * 0xFF51AFD7ED558CCDull);
-        for (u64 j = 0; j < ((len + 7) >> 3); j++) { h = (h ^ T.arena[unit + 1 + j]) * 0x9FB21C651E98DF25ull; h ^= h >> 32; }
-        h = mix64(h);
-        u64 slot = h & mask;
-        for (;;) { // distinct words only: claim the first free slot
-            if (atomicCAS(&T.l_refs[slot], 0ull, r) == 0) break;
-            slot = (slot + 1) & mask;
-        }
-        T.l_counts[slot] = counts[i];
-        T.l_finv[slot] = finv[i];
-    }
+    const u32 w_wnew = __reduce_add_sync(0xFFFFFFFFu, n_wnew);
+    if (lane == 0 && w_wnew) atomicAdd(&st->w_entries, (u64)w_wnew);
 }
 
 } // namespace wc

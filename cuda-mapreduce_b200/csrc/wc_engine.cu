@@ -71,16 +71,17 @@ static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static int alloc_tables(wc_engine *e, u32 s_log2, u32 l_log2, u64 arena_bytes, wc::Tables *out, void **block,
                         size_t *block_bytes) {
+    // word table (1..16 bytes): 16-byte keys | counts | ~first;  long table (17+): refs | counts | ~first
     const size_t s_n = (size_t)1 << s_log2, l_n = (size_t)1 << l_log2;
-    const size_t bytes = (3 * s_n + 3 * l_n) * sizeof(u64);
+    const size_t bytes = (4 * s_n + 3 * l_n) * sizeof(u64);
     void *p = nullptr;
     CK(cudaMalloc(&p, bytes));
     u64 *q = (u64 *)p;
     wc::Tables T = e->T;
-    T.s_keys = q; T.s_counts = q + s_n; T.s_finv = q + 2 * s_n;
-    q += 3 * s_n;
-    T.l_refs = q; T.l_counts = q + l_n; T.l_finv = q + 2 * l_n;
-    T.s_log2 = s_log2; T.l_log2 = l_log2;
+    T.w_keys = (ulonglong2 *)q; T.w_counts = q + 2 * s_n; T.w_finv = q + 3 * s_n;
+    q += 4 * s_n;
+    T.x_refs = q; T.x_counts = q + l_n; T.x_finv = q + 2 * l_n;
+    T.w_log2 = s_log2; T.x_log2 = l_log2;
     if (T.arena == nullptr) {
         const u64 units = arena_bytes / 8;
         CK(cudaMalloc((void **)&T.arena, units * 8));
@@ -113,7 +114,7 @@ void wc_config_default(wc_config *cfg) {
     cfg->path = WC_PATH_AUTO;
     cfg->chunk_bytes = 64ull << 20;
     cfg->short_table_log2 = 21;
-    cfg->long_table_log2 = 21;
+    cfg->long_table_log2 = 18;
     cfg->arena_bytes = 256ull << 20;
 }
 
@@ -152,9 +153,9 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     wc_config &c = e->cfg;
     if (c.chunk_bytes == 0) c.chunk_bytes = 64ull << 20;
     if (c.short_table_log2 == 0) c.short_table_log2 = 21;
-    if (c.long_table_log2 == 0) c.long_table_log2 = 21;
+    if (c.long_table_log2 == 0) c.long_table_log2 = 18;
     if (c.arena_bytes == 0) c.arena_bytes = 256ull << 20;
-    if (c.short_table_log2 < 10 || c.short_table_log2 > 34 || c.long_table_log2 < 10 || c.long_table_log2 > 34 ||
+    if (c.short_table_log2 < 10 || c.short_table_log2 > 32 || c.long_table_log2 < 10 || c.long_table_log2 > 34 ||
         c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT)) {
         e->err = "wc_config out of range";
         return WC_ERR_INVALID;
@@ -386,40 +387,41 @@ int wc_finish(wc_engine *e, wc_result **out) {
     const wc::Status st = *e->h_status;
     if (st.err) {
         char msg[160];
-        snprintf(msg, sizeof(msg), "device tables full (flags 0x%x: short=%llu long=%llu arena=%llu units)", st.err,
-                 (unsigned long long)st.s_entries, (unsigned long long)st.l_entries, (unsigned long long)st.arena_used);
+        snprintf(msg, sizeof(msg), "device tables full (flags 0x%x: words=%llu long=%llu arena=%llu units)", st.err,
+                 (unsigned long long)st.w_entries, (unsigned long long)st.x_entries, (unsigned long long)st.arena_used);
         e->err = msg;
         return WC_ERR_TABLE_FULL;
     }
 
     // ---- bring the tables to the host
-    const size_t s_n = (size_t)1 << e->T.s_log2, l_n = (size_t)1 << e->T.l_log2;
-    std::vector<u64> tab((3 * s_n + 3 * l_n));
+    const size_t s_n = (size_t)1 << e->T.w_log2, l_n = (size_t)1 << e->T.x_log2;
+    std::vector<u64> tab((4 * s_n + 3 * l_n));
     CK(cudaMemcpyAsync(tab.data(), e->table_block, tab.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
     std::vector<u64> arena((size_t)st.arena_used);
     if (st.arena_used > 1)
         CK(cudaMemcpyAsync(arena.data(), e->T.arena, arena.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
 
-    const u64 *s_keys = tab.data(), *s_counts = s_keys + s_n, *s_finv = s_keys + 2 * s_n;
-    const u64 *l_refs = tab.data() + 3 * s_n, *l_counts = l_refs + l_n, *l_finv = l_refs + 2 * l_n;
+    const u64 *w_keys = tab.data(), *w_counts = w_keys + 2 * s_n, *w_finv = w_keys + 3 * s_n;
+    const u64 *x_refs = tab.data() + 4 * s_n, *x_counts = x_refs + l_n, *x_finv = x_refs + 2 * l_n;
     std::string blob;
     std::vector<wc::HostEntry> entries;
-    entries.reserve((size_t)(st.s_entries + st.l_entries));
+    entries.reserve((size_t)(st.w_entries + st.x_entries));
     for (size_t i = 0; i < s_n; i++) {
-        const u64 k = s_keys[i];
-        if (k == 0 || (int64_t)s_counts[i] == 0) continue;
-        u32 len = 8;
-        while (len > 1 && ((k >> (8 * (len - 1))) & 0xFF) == 0) len--;
-        entries.push_back(wc::HostEntry{blob.size(), len, (int64_t)s_counts[i], ~s_finv[i]});
-        blob.append((const char *)&k, len);
+        const u64 k[2] = {w_keys[2 * i], w_keys[2 * i + 1]};
+        if (k[0] == 0 || (int64_t)w_counts[i] == 0) continue;
+        const unsigned char *kb = (const unsigned char *)k; // the word itself, zero padded to 16
+        u32 len = 16;
+        while (len > 1 && kb[len - 1] == 0) len--;
+        entries.push_back(wc::HostEntry{blob.size(), len, (int64_t)w_counts[i], ~w_finv[i]});
+        blob.append((const char *)kb, len);
     }
     for (size_t i = 0; i < l_n; i++) {
-        const u64 r = l_refs[i];
-        if (r == 0 || (int64_t)l_counts[i] == 0) continue;
+        const u64 r = x_refs[i];
+        if (r == 0 || (int64_t)x_counts[i] == 0) continue;
         const u64 unit = r & ((1ull << 40) - 1);
         const u64 len = arena[unit];
-        entries.push_back(wc::HostEntry{blob.size(), (u32)len, (int64_t)l_counts[i], ~l_finv[i]});
+        entries.push_back(wc::HostEntry{blob.size(), (u32)len, (int64_t)x_counts[i], ~x_finv[i]});
         blob.append((const char *)&arena[unit + 1], (size_t)len);
     }
 
@@ -512,8 +514,8 @@ __global__ void static_begin_kernel(wc::Status *st) {
 __global__ void static_end_kernel(const wc::Status *st, u64 *out) {
     if (threadIdx.x == 0) {
         out[0] = st->n_flush; out[1] = st->n_empty; out[2] = st->stop; out[3] = st->p0;
-        out[4] = st->lost_empty; out[5] = st->p0_found; out[6] = st->err; out[7] = st->s_entries;
-        out[8] = st->l_entries; out[9] = st->arena_used; out[10] = st->n_long; out[11] = st->n_spill;
+        out[4] = st->lost_empty; out[5] = st->p0_found; out[6] = st->err; out[7] = st->w_entries;
+        out[8] = st->x_entries; out[9] = st->arena_used; out[10] = st->n_long; out[11] = st->n_spill;
     }
 }
 
@@ -533,11 +535,11 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
                                       void *stream_handle) {
     g_static_err[0] = 0;
     if (device < 0 || device >= kStaticMaxDevices || (!dev_text && n) || !dev_short_table || !dev_long_table ||
-        !dev_arena || !dev_counters || short_log2 < 10 || short_log2 > 34 || long_log2 < 10 || long_log2 > 34 ||
+        !dev_arena || !dev_counters || short_log2 < 10 || short_log2 > 32 || long_log2 < 10 || long_log2 > 34 ||
         arena_bytes < 4096)
         return static_fail(WC_ERR_INVALID, "wc_count_device_static: bad argument", cudaSuccess);
-    if (((uintptr_t)dev_text & 15) != 0)
-        return static_fail(WC_ERR_UNALIGNED, "wc_count_device_static: text must be 16-byte aligned", cudaSuccess);
+    if (((uintptr_t)dev_text & 15) != 0 || ((uintptr_t)dev_short_table & 15) != 0)
+        return static_fail(WC_ERR_UNALIGNED, "wc_count_device_static: text and short table must be 16-byte aligned", cudaSuccess);
     if (n > (size_t)WC_STATIC_MAX_BYTES)
         return static_fail(WC_ERR_TOO_LARGE, "wc_count_device_static: text larger than WC_STATIC_MAX_BYTES", cudaSuccess);
 
@@ -573,12 +575,13 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
         wc::WarpSummary *ws = (wc::WarpSummary *)(sd.scratch + kStaticStatusBytes);
         const size_t s_n = (size_t)1 << short_log2, l_n = (size_t)1 << long_log2;
         wc::Tables T;
-        T.s_keys = (u64 *)dev_short_table; T.s_counts = T.s_keys + s_n; T.s_finv = T.s_keys + 2 * s_n; T.s_log2 = short_log2;
-        T.l_refs = (u64 *)dev_long_table; T.l_counts = T.l_refs + l_n; T.l_finv = T.l_refs + 2 * l_n; T.l_log2 = long_log2;
+        T.w_keys = (ulonglong2 *)dev_short_table; T.w_counts = (u64 *)dev_short_table + 2 * s_n;
+        T.w_finv = (u64 *)dev_short_table + 3 * s_n; T.w_log2 = short_log2;
+        T.x_refs = (u64 *)dev_long_table; T.x_counts = T.x_refs + l_n; T.x_finv = T.x_refs + 2 * l_n; T.x_log2 = long_log2;
         T.arena = (u64 *)dev_arena; T.arena_units = arena_bytes / 8; T.st = st;
 
         // results start from zero; the shared working state is re-initialised on every call
-        if ((ce = cudaMemsetAsync(dev_short_table, 0, 3 * s_n * sizeof(u64), stream)) != cudaSuccess ||
+        if ((ce = cudaMemsetAsync(dev_short_table, 0, 4 * s_n * sizeof(u64), stream)) != cudaSuccess ||
             (ce = cudaMemsetAsync(dev_long_table, 0, 3 * l_n * sizeof(u64), stream)) != cudaSuccess) {
             rc = static_fail(WC_ERR_CUDA, "cudaMemsetAsync", ce); break;
         }

@@ -63,9 +63,9 @@ typedef struct wc_config {
     int32_t mode;              /* WC_MODE_* */
     int32_t path;              /* WC_PATH_* */
     uint64_t chunk_bytes;      /* wc_feed() streaming chunk (0: 64 MiB) */
-    uint32_t short_table_log2; /* global table slots for words <= 8 bytes (0: 2^21) */
-    uint32_t long_table_log2;  /* global table slots for longer words (0: 2^21) */
-    uint64_t arena_bytes;      /* device byte store for longer words (0: 256 MiB) */
+    uint32_t short_table_log2; /* global table slots for words of 1..16 bytes (0: 2^21; at most 32) */
+    uint32_t long_table_log2;  /* global table slots for words of 17+ bytes (0: 2^18) */
+    uint64_t arena_bytes;      /* device byte store for the 17+ byte words (0: 256 MiB) */
     uint64_t base_offset;      /* offset of this engine's first byte in the whole input (shards) */
     uint32_t flags;            /* reserved, 0 */
     uint32_t reserved;
@@ -79,9 +79,9 @@ typedef struct wc_stats {
     uint64_t n_lost_empty;   /* empties before the first non-empty word (lost, main.cu:81,103) */
     uint64_t stop;           /* offset at which input processing stopped (main.cu:185), == bytes if none */
     uint64_t n_distinct;     /* distinct non-empty words counted */
-    uint64_t n_long_words;   /* words > 8 bytes (long-word path) */
+    uint64_t n_long_words;   /* words of 9+ bytes (they bypass the shared-memory table) */
     uint64_t n_spilled;      /* short words that bypassed the shared-memory table */
-    uint64_t n_slow_tiles;   /* 512-byte tiles that needed the CR / NUL line-state path */
+    uint64_t n_slow_tiles;   /* 1 KiB tiles that held a control byte and took the exact line-state path */
     uint64_t table_grows;    /* times a device table was re-hashed into a larger one */
     double device_ms;        /* device time of this job's kernels (CUDA events on the engine's stream) */
     double count_kernel_ms;  /* of which the tokenizer/count kernel alone */
@@ -156,11 +156,11 @@ WC_API void *wc_stream(wc_engine *e);
  *
  *   dev_text          n bytes of text in device memory, 16-byte aligned; the WHOLE input (it is
  *                     treated as starting at a line start and ending the input).
- *   dev_short_table   3 << short_log2 uint64: keys | counts | ~first-offset of words of 1..8 bytes
- *                     (a key is the word itself, little-endian, zero padded).
- *   dev_long_table    3 << long_log2 uint64: refs | counts | ~first-offset of longer words; a ref is
- *                     (24-bit tag << 40) | unit index into dev_arena.
- *   dev_arena         arena_bytes of storage for the longer words: unit[i] = length in bytes,
+ *   dev_short_table   4 << short_log2 uint64, 16-byte aligned: keys (2 per slot) | counts | ~first-offset
+ *                     of words of 1..16 bytes (a key is the word itself, zero padded to 16 bytes).
+ *   dev_long_table    3 << long_log2 uint64: refs | counts | ~first-offset of words of 17+ bytes; a
+ *                     ref is (24-bit tag << 40) | unit index into dev_arena.
+ *   dev_arena         arena_bytes of storage for the 17+ byte words: unit[i] = length in bytes,
  *                     unit[i+1...] = the bytes, zero padded to 8.
  *   dev_counters      WC_STATIC_COUNTERS uint64 written at the end: n_flush, n_empty, stop (~0 if
  *                     none), p0 (~0 if none), lost_empty, p0_found, err (0 = ok, else a table or the

@@ -30,11 +30,12 @@ def decode_tables(short, long_, arena):
     """{word: (count, first_offset)} from the raw device tables (layout: include/wc.h)."""
     out = {}
     s_n, l_n = 1 << S_LOG2, 1 << L_LOG2
-    keys, counts, finv = short[:s_n], short[s_n:2 * s_n], short[2 * s_n:]
-    for i in np.nonzero(keys)[0]:
+    keys, counts, finv = short[:2 * s_n], short[2 * s_n:3 * s_n], short[3 * s_n:]
+    kraw = keys.tobytes()
+    for i in np.nonzero(keys[0::2])[0]:
         if counts[i] == 0:
             continue
-        word = int(keys[i]).to_bytes(8, "little").rstrip(b"\0")
+        word = kraw[16 * i:16 * i + 16].rstrip(b"\0")
         out[word] = (int(counts[i]), NONE - int(finv[i]))
     refs, counts, finv = long_[:l_n], long_[l_n:2 * l_n], long_[2 * l_n:]
     raw = arena.tobytes()
@@ -65,7 +66,7 @@ def test_static_entry_point_matches_engine_twice_in_a_row():
     rng = random.Random(31)
     first = random_text(rng, 40000, weird=0.02)            # CR / NUL / blank lines included
     second = random_text(rng, 3000, weird=0.0).replace(b"\n\n", b"\n") + b"unterminated tail"
-    bufs = (torch.empty(3 << S_LOG2, dtype=torch.int64, device="cuda"),
+    bufs = (torch.empty(4 << S_LOG2, dtype=torch.int64, device="cuda"),
             torch.empty(3 << L_LOG2, dtype=torch.int64, device="cuda"),
             torch.empty(ARENA // 8, dtype=torch.int64, device="cuda"),
             torch.empty(12, dtype=torch.int64, device="cuda"))
