@@ -22,15 +22,15 @@ constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 
 constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = 16;                 // warps per CTA
 constexpr int kThreads = kWarps * 32;
-constexpr u32 kSmemEntries = 9792;         // 16-byte entries of the per-CTA table (153 KiB)
+constexpr u32 kSmemEntries = 10304;        // 16-byte entries of the per-CTA table (161 KiB)
 constexpr int kBufBytes = 1072;            // one tile buffer: 16 B tail of the previous tile + tile + slack
 constexpr int kRingBytes = 2 * kBufBytes;  // per warp: two buffers, the next tile lands by cp.async
 constexpr int kDlCap = 512;                // per warp: delimiter list entries
 constexpr int kDlBytes = kDlCap * 2;
-constexpr int kQueue = 64;                 // per warp: deferred words (16-byte key + 8-byte record)
+constexpr int kQueue = 64;                 // per warp: deferred words (16-byte records)
 constexpr u64 kNone = ~0ull;
 
-constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kQueue * 24;
+constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kQueue * 16;
 constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16;
 constexpr size_t kSmemTotal = kSmemTableBytes + (size_t)kWarps * kWarpSmemBytes;
 static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
@@ -389,31 +389,48 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
     return o;
 }
 
-// Deferred words: words of 1..8 bytes the CTA's table had no room for, and every word of 9+ bytes.
-// A record is the word's first 16 bytes plus (end offset relative to the CTA's range, length).
-// They are inserted into the global tables 32 at a time, so that every lane has its global-memory
-// accesses in flight at once instead of the whole warp waiting on two or three.
-// Returns new word-table slots | new long-table slots << 16.
-__device__ __noinline__ u32 drain_deferred(uint4 *qk, uint2 *qm, u32 count, u32 take, const Launch *Lp,
-                                           const Tables *Tp, u64 cta_base) {
+// Deferred words: words of 1..8 bytes that missed in the CTA's table, and every word of 9+ bytes.
+// A record is (first 8 bytes, end offset relative to the CTA's range, length).  They are handled 32
+// at a time, away from the hot loop, so that every lane has its global-memory accesses in flight at
+// once instead of the whole warp waiting on two or three:
+//   1..8 bytes  : claim the word's shared-memory slot if it is still free (this is how the CTA's
+//                 table fills up), else count it in the global word table;
+//   9..16 bytes : fetch bytes 8..15 from the text, count in the global word table;
+//   17+ bytes   : the arena-backed long table.
+// Returns new word-table slots | new long-table slots << 16 | short words sent to the global table << 24.
+__device__ __noinline__ u32 drain_deferred(uint4 *q, u32 count, u32 take, const Launch *Lp, const Tables *Tp,
+                                           u64 cta_base, uint4 *tab) {
     const u32 lane = lane_id();
     u32 made = 0;
     if (lane < take) {
-        const uint4 k = qk[lane];
-        const uint2 rec = qm[lane];
-        const u64 end = cta_base + rec.x; // buffer-relative offset of the delimiter
+        const uint4 rec = q[lane];
+        const u32 len = rec.w;
+        const u64 end = cta_base + rec.z; // buffer-relative offset of the delimiter
         const u64 delta = Lp->negate ? ~0ull : 1ull;
-        if (rec.y <= 16)
-            made = word_insert(*Tp, (u64)k.x | ((u64)k.y << 32), (u64)k.z | ((u64)k.w << 32), delta, Lp->base + end);
-        else
-            made = long_insert(Tp, Lp->buf, end - rec.y, rec.y, delta, Lp->base + end) << 16;
+        const u64 k0 = (u64)rec.x | ((u64)rec.y << 32);
+        if (len <= 8) {
+            const u32 slot = __umulhi(hash32(rec.x, rec.y), kSmemEntries);
+            const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[slot]), 0ull, k0);
+            if (old == 0 || old == k0) {
+                u32 *cell = reinterpret_cast<u32 *>(&tab[slot]);
+                atomicAdd(cell + 2, (u32)delta);
+                atomicMin(cell + 3, rec.z);
+            } else {
+                made = word_insert(*Tp, k0, 0ull, delta, Lp->base + end) | (1u << 24);
+            }
+        } else if (len <= 16) {
+            const u64 k1 = load8_unaligned(Lp->buf, end - len + 8, len - 8);
+            made = word_insert(*Tp, k0, k1, delta, Lp->base + end);
+        } else {
+            made = long_insert(Tp, Lp->buf, end - len, len, delta, Lp->base + end) << 16;
+        }
     }
     __syncwarp();
-    uint4 mk = make_uint4(0, 0, 0, 0); uint2 mm = make_uint2(0, 0);
+    uint4 mv = make_uint4(0, 0, 0, 0);
     const bool keep = lane + take < count;
-    if (keep) { mk = qk[lane + take]; mm = qm[lane + take]; }
+    if (keep) mv = q[lane + take];
     __syncwarp();
-    if (keep) { qk[lane] = mk; qm[lane] = mm; }
+    if (keep) q[lane] = mv;
     __syncwarp();
     return made;
 }
@@ -443,9 +460,14 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     unsigned char *warp_all = wc_smem + kSmemTableBytes;
     __shared__ u32 s_first_ws;
     __shared__ u64 s_stop;
+    __shared__ uint2 s_keep[17]; // s_keep[n]: mask that keeps the first n bytes of an 8-byte key (n >= 8: all)
 
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     Status *st = T.st;
+    if (tid < 17) {
+        const u64 m = tid >= 8 ? ~0ull : ((1ull << (8 * tid)) - 1);
+        s_keep[tid] = make_uint2((u32)m, (u32)(m >> 32));
+    }
 
     // ---- which part of the piece does this launch cover?  (One thread reads STOP so that the
     // whole CTA takes the same branch even while other CTAs are still lowering it.)
@@ -489,11 +511,10 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     for (u32 i = tid; i < kSmemEntries; i += kThreads) tab[i] = make_uint4(0, 0, 0, 0xFFFFFFFFu);
     __syncthreads();
 
-    // per-warp shared memory: [two tile buffers] [delimiter list] [deferred keys] [deferred records]
+    // per-warp shared memory: [two tile buffers] [delimiter list] [deferred words]
     unsigned char *wbase = warp_all + warp * kWarpSmemBytes;
     unsigned short *dl = reinterpret_cast<unsigned short *>(wbase + kRingBytes);
-    uint4 *dqk = reinterpret_cast<uint4 *>(wbase + kRingBytes + kDlBytes);
-    uint2 *dqm = reinterpret_cast<uint2 *>(wbase + kRingBytes + kDlBytes + kQueue * 16);
+    uint4 *dq = reinterpret_cast<uint4 *>(wbase + kRingBytes + kDlBytes);
 
     const u32 tiles_total = (u32)((L.n + kTile - 1) / kTile);
     const u32 gwarp = blockIdx.x * kWarps + warp;
@@ -506,8 +527,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     }
     const u32 lt_mask = (1u << lane) - 1;
 
-    u32 n_made = 0;                                  // new global slots: word table | long table << 16
-    u32 n_long = 0, n_spill = 0;
+    u32 n_wnew = 0, n_xnew = 0, n_spill = 0, n_long = 0; // per lane: new global slots, misses, 9+ byte words
     u32 acc_flush = 0, acc_empty = 0, acc_slow = 0;  // per lane; a warp's range is < 4 GiB
     u32 q_count = 0;
     bool seen_nonempty = L.negate != 0;              // roll-back launches do not look for P0
@@ -670,7 +690,8 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                 __syncwarp();
                 const u32 total = dense ? (ph ? totB : totA) : totA + totB;
 
-                // ---- one word per lane; straight-line code, the rare cases are deferred
+                // ---- one word per lane: a hit in the CTA's table is counted here, everything else
+                // (misses, words of 9+ bytes) is queued for drain_deferred()
                 for (u32 k0 = 0; k0 < total; k0 += 32) {
                     const u32 k = k0 + lane;
                     const u32 d = k < total ? (u32)dl[k] : 0u;
@@ -680,29 +701,20 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const int prev = lane ? (int)(d_up & 0x3FFu) : before;
                     const int len = e - prev - 1;
                     const bool word = (d >> 15) && len > 0;       // a flush of a non-empty word
-                    const bool is_short = word && len <= 8;
                     const int rlen = len > 16 ? 16 : (len < 1 ? 1 : len); // bytes looked at (keeps reads in bounds)
 
                     // key = the word's first 8 bytes, from the warp's shared-memory copy of the tile
                     const u32 idx = (u32)(16 + e - rlen);          // >= 0: reaches into the previous tile's tail
                     const u32 *r = ring32 + (idx >> 2);
                     const u32 w0 = r[0], w1 = r[1], w2 = r[2];
+                    const uint2 keep = s_keep[rlen];
                     const u32 sh = (idx & 3) * 8;
-                    u32 klo = __funnelshift_r(w0, w1, sh), khi = __funnelshift_r(w1, w2, sh);
-                    const u32 nb8 = 8 * (u32)rlen;
-                    klo &= nb8 >= 32 ? 0xFFFFFFFFu : ((1u << nb8) - 1);
-                    khi &= nb8 >= 64 ? 0xFFFFFFFFu : (nb8 > 32 ? ((1u << (nb8 - 32)) - 1) : 0u);
+                    const u32 klo = __funnelshift_r(w0, w1, sh) & keep.x, khi = __funnelshift_r(w1, w2, sh) & keep.y;
 
-                    // single-probe shared-memory table: hit, claim an empty slot, or defer
+                    // single-probe shared-memory table
                     const u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);
-                    uint4 ent = tab[slot];
-                    bool hit = is_short && ent.x == klo && ent.y == khi;
-                    if (is_short && !hit && (ent.x | ent.y) == 0) { // only while the table fills up
-                        const u64 key = (u64)klo | ((u64)khi << 32);
-                        const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[slot]), 0ull, key);
-                        hit = old == 0 || old == key;
-                        ent.w = 0xFFFFFFFFu;
-                    }
+                    const uint4 ent = tab[slot];
+                    const bool hit = word && len <= 8 && ent.x == klo && ent.y == khi;
                     const u32 rel = relT + (u32)e;
                     u32 *cell = reinterpret_cast<u32 *>(&tab[slot]);
                     if (hit) atomicAdd(cell + 2, delta32);
@@ -711,25 +723,13 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const bool defer = word && !hit;
                     const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
                     if (bq) {
-                        if (defer) {
-                            u32 k1lo = 0, k1hi = 0;
-                            if (len > 8) { // bytes 8..15 of a longer word
-                                const u32 w3 = r[3], w4 = r[4];
-                                k1lo = __funnelshift_r(w2, w3, sh); k1hi = __funnelshift_r(w3, w4, sh);
-                                const u32 mb = nb8 - 64; // 8..64 bits
-                                k1lo &= mb >= 32 ? 0xFFFFFFFFu : ((1u << mb) - 1);
-                                k1hi &= mb >= 64 ? 0xFFFFFFFFu : (mb > 32 ? ((1u << (mb - 32)) - 1) : 0u);
-                            }
-                            const u32 qi = q_count + __popc(bq & lt_mask);
-                            dqk[qi] = make_uint4(klo, khi, k1lo, k1hi);
-                            dqm[qi] = make_uint2(rel, (u32)len);
-                            n_long += !is_short;
-                            n_spill += is_short;
-                        }
+                        if (defer) dq[q_count + __popc(bq & lt_mask)] = make_uint4(klo, khi, rel, (u32)len);
+                        n_long += defer && len > 8;
                         q_count += __popc(bq);
                         __syncwarp();
                         if (q_count >= 32) {
-                            n_made += drain_deferred(dqk, dqm, q_count, 32, &L, &T, cta_base);
+                            const u32 made = drain_deferred(dq, q_count, 32, &L, &T, cta_base, tab);
+                            n_wnew += made & 1u; n_xnew += (made >> 16) & 1u; n_spill += made >> 24;
                             q_count -= 32;
                         }
                     }
@@ -740,12 +740,15 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             // the next tile sees this tile's last delimiter at a negative position
             carry_prev = first_prev - kTile < -(1 << 30) ? -(1 << 30) : first_prev - kTile;
         }
-        if (q_count > 0) n_made += drain_deferred(dqk, dqm, q_count, q_count, &L, &T, cta_base);
+        if (q_count > 0) {
+            const u32 made = drain_deferred(dq, q_count, q_count, &L, &T, cta_base, tab);
+            n_wnew += made & 1u; n_xnew += (made >> 16) & 1u; n_spill += made >> 24;
+        }
     }
 
     // ---- per-warp results
     const u64 w_flush = warp_sum64(acc_flush), w_empty = warp_sum64(acc_empty);
-    const u32 w_xnew = __reduce_add_sync(0xFFFFFFFFu, n_made >> 16);
+    const u32 w_xnew = __reduce_add_sync(0xFFFFFFFFu, n_xnew);
     const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, n_long), w_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
     if (lane == 0) {
         if (w_flush) atomicAdd(&st->n_flush, L.negate ? (u64)(-(long long)w_flush) : w_flush);
@@ -765,7 +768,6 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
 
     // ---- flush the CTA's table into the global one
     __syncthreads();
-    u32 n_wnew = n_made & 0xFFFFu;
     for (u32 i = tid; i < kSmemEntries; i += kThreads) {
         const uint4 ent = tab[i];
         if ((ent.x | ent.y) != 0 && ent.z != 0) {
