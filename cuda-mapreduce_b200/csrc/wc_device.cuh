@@ -692,7 +692,11 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
 
                 // ---- one word per lane: a hit in the CTA's table is counted here, everything else
                 // (misses, words of 9+ bytes) is queued for drain_deferred()
+#ifdef WC_EXP_NOROUNDS
+                for (u32 k0 = 0; k0 < total && relT == 0xFFFFFFF1u; k0 += 32) {
+#else
                 for (u32 k0 = 0; k0 < total; k0 += 32) {
+#endif
                     const u32 k = k0 + lane;
                     const u32 d = k < total ? (u32)dl[k] : 0u;
                     const u32 d_up = __shfl_up_sync(0xFFFFFFFFu, d, 1);
@@ -717,10 +721,18 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const bool hit = word && len <= 8 && ent.x == klo && ent.y == khi;
                     const u32 rel = relT + (u32)e;
                     u32 *cell = reinterpret_cast<u32 *>(&tab[slot]);
+#ifndef WC_EXP_NOATOM
                     if (hit) atomicAdd(cell + 2, delta32);
                     if (hit && rel < ent.w) atomicMin(cell + 3, rel);
+#else
+                    if (hit && rel == 0xFFFFFFF1u) atomicAdd(cell + 2, delta32);
+#endif
 
+#ifdef WC_EXP_NODEFER
+                    const bool defer = false;
+#else
                     const bool defer = word && !hit;
+#endif
                     const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
                     if (bq) {
                         if (defer) dq[q_count + __popc(bq & lt_mask)] = make_uint4(klo, khi, rel, (u32)len);
@@ -728,8 +740,10 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                         q_count += __popc(bq);
                         __syncwarp();
                         if (q_count >= 32) {
+#ifndef WC_EXP_NODRAIN
                             const u32 made = drain_deferred(dq, q_count, 32, &L, &T, cta_base, tab);
                             n_wnew += made & 1u; n_xnew += (made >> 16) & 1u; n_spill += made >> 24;
+#endif
                             q_count -= 32;
                         }
                     }

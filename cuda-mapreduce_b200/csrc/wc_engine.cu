@@ -464,6 +464,8 @@ extern "C" int wc_debug_classify16(const uint8_t *bytes16, uint32_t *delim_mask,
     return WC_OK;
 }
 
+extern "C" uint32_t wc_debug_smem_entries(void) { return wc::kSmemEntries; }
+
 extern "C" uint32_t wc_debug_smem_slot(uint64_t key) {
     return (uint32_t)(((uint64_t)wc::hash32((u32)key, (u32)(key >> 32)) * wc::kSmemEntries) >> 32);
 }

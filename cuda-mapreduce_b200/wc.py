@@ -11,7 +11,7 @@ MODE_EXACT = 1
 
 
 def lib_path():
-    return os.path.join(HERE, "libwc.so")
+    return os.environ.get("WC_LIB") or os.path.join(HERE, "libwc.so")
 
 
 def build(force=False):

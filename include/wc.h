@@ -198,6 +198,7 @@ WC_API int wc_debug_finalize(const char *words, const uint32_t *lens, const int6
 WC_API int wc_debug_classify16(const uint8_t *bytes16, uint32_t *delim_mask, uint32_t *lf_mask,
                                uint32_t *kill_mask);
 WC_API uint32_t wc_debug_smem_slot(uint64_t key);
+WC_API uint32_t wc_debug_smem_entries(void);
 
 #ifdef __cplusplus
 }

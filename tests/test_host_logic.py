@@ -66,7 +66,7 @@ def test_smem_slot_hash_spreads_short_words():
     while len(words) < 4000:
         words.add(bytes(rng.choice(b"abcdefghijklmnopqrstuvwxyz") for _ in range(rng.randint(1, 8))))
     slots = set(L.wc_debug_smem_slot(int.from_bytes(w, "little")) for w in words)
-    m, n = 9792, len(words)
+    m, n = L.wc_debug_smem_entries(), len(words)
     assert max(slots) < m
     ideal = m * (1 - (1 - 1 / m) ** n)  # distinct slots a uniform hash would hit
     assert len(slots) > 0.97 * ideal
