@@ -22,12 +22,13 @@ constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 
 constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = 16;                 // warps per CTA
 constexpr int kThreads = kWarps * 32;
-constexpr u32 kSmemEntries = 10304;        // 16-byte entries of the per-CTA table (161 KiB)
+constexpr u32 kSmemEntries = 8768;         // 16-byte entries of the per-CTA table (137 KiB)
 constexpr int kBufBytes = 1072;            // one tile buffer: 16 B tail of the previous tile + tile + slack
 constexpr int kRingBytes = 2 * kBufBytes;  // per warp: two buffers, the next tile lands by cp.async
 constexpr int kDlCap = 512;                // per warp: delimiter list entries
 constexpr int kDlBytes = kDlCap * 2;
-constexpr int kQueue = 64;                 // per warp: deferred words (16-byte records)
+constexpr int kDrainBatch = 128;           // deferred words handled per drain: four per lane
+constexpr int kQueue = kDrainBatch + 32;   // per warp: deferred words (16-byte records)
 constexpr u64 kNone = ~0ull;
 
 constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kQueue * 16;
@@ -185,14 +186,22 @@ __device__ __forceinline__ ulonglong2 cas128(ulonglong2 *addr, ulonglong2 cmp, u
     return old;
 }
 
+// Home slot of a word of 1..16 bytes in the global word table: a function of its first 8 bytes and
+// its length only, so that it is known before bytes 8..15 have been fetched.
+__device__ __forceinline__ u32 word_home(const Tables &T, u64 k0, u32 len) {
+    return hash_key128((u32)k0, (u32)(k0 >> 32), len, 0x5bd1e995u) >> (32 - T.w_log2);
+}
+
+__device__ __forceinline__ u32 key_len8(u64 k0) { return 8u - ((u32)__clzll(k0) >> 3); } // bytes used, k0 != 0
+
 // Adds `delta` occurrences of a word of 1..16 bytes (k0 = bytes 0..7, k1 = bytes 8..15, zero padded)
-// to the global table; returns 1 if it claimed a new slot.
-__device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u64 delta, u64 first_abs) {
+// to the global table, probing from `slot` whose key the caller has already loaded (`k`).
+// Returns 1 if it claimed a new slot.
+__device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u64 delta, u64 first_abs, u32 slot,
+                                              ulonglong2 k) {
     const u32 mask = (u32)((1ull << T.w_log2) - 1);
-    u32 slot = hash_key128((u32)k0, (u32)(k0 >> 32), (u32)k1, (u32)(k1 >> 32)) >> (32 - T.w_log2);
     u32 is_new = 0;
     for (u32 probes = 0;; ++probes) {
-        ulonglong2 k = __ldcg(&T.w_keys[slot]);
         if (k.x == 0) { // a used slot never has k.x == 0: a word's first byte is not 0x00
             k = cas128(&T.w_keys[slot], make_ulonglong2(0, 0), make_ulonglong2(k0, k1));
             if (k.x == 0) { is_new = 1; k.x = k0; k.y = k1; }
@@ -200,10 +209,16 @@ __device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u64 
         if (k.x == k0 && k.y == k1) break;
         slot = (slot + 1) & mask;
         if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrWordFull); return 0; }
+        k = __ldcg(&T.w_keys[slot]);
     }
     atomicAdd(&T.w_counts[slot], delta); // both fire-and-forget (RED)
     atomicMax(&T.w_finv[slot], ~first_abs);
     return is_new;
+}
+
+__device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u32 len, u64 delta, u64 first_abs) {
+    const u32 slot = word_home(T, k0, len);
+    return word_insert_at(T, k0, k1, delta, first_abs, slot, __ldcg(&T.w_keys[slot]));
 }
 
 // -------------------------------------------------------- global long table (17+ bytes)
@@ -390,48 +405,69 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
 }
 
 // Deferred words: words of 1..8 bytes that missed in the CTA's table, and every word of 9+ bytes.
-// A record is (first 8 bytes, end offset relative to the CTA's range, length).  They are handled 32
-// at a time, away from the hot loop, so that every lane has its global-memory accesses in flight at
-// once instead of the whole warp waiting on two or three:
+// A record is (first 8 bytes, end offset relative to the CTA's range, length).  They are handled
+// kDrainBatch at a time, away from the hot loop, four per lane, and every global-memory read of the
+// batch is issued before the first one is used, so that the warp waits for one round trip, not for
+// one per word:
 //   1..8 bytes  : claim the word's shared-memory slot if it is still free (this is how the CTA's
 //                 table fills up), else count it in the global word table;
 //   9..16 bytes : fetch bytes 8..15 from the text, count in the global word table;
 //   17+ bytes   : the arena-backed long table.
-// Returns new word-table slots | new long-table slots << 16 | short words sent to the global table << 24.
+// Returns new word-table slots | new long-table slots << 8 | short words sent to the global table << 16.
 __device__ __noinline__ u32 drain_deferred(uint4 *q, u32 count, u32 take, const Launch *Lp, const Tables *Tp,
                                            u64 cta_base, uint4 *tab) {
     const u32 lane = lane_id();
+    const Tables &T = *Tp;
+    const u64 delta = Lp->negate ? ~0ull : 1ull;
+    constexpr int R = kDrainBatch / 32;
+    uint4 rec[R];
+    u32 slot[R];
+    ulonglong2 key[R];
+    u64 k1[R];
+    u32 todo = 0; // bit j: record j goes to the global word table
     u32 made = 0;
-    if (lane < take) {
-        const uint4 rec = q[lane];
-        const u32 len = rec.w;
-        const u64 end = cta_base + rec.z; // buffer-relative offset of the delimiter
-        const u64 delta = Lp->negate ? ~0ull : 1ull;
-        const u64 k0 = (u64)rec.x | ((u64)rec.y << 32);
-        if (len <= 8) {
-            const u32 slot = __umulhi(hash32(rec.x, rec.y), kSmemEntries);
-            const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[slot]), 0ull, k0);
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+        rec[j] = lane + 32 * j < take ? q[lane + 32 * j] : make_uint4(0, 0, 0, 0);
+        const u32 len = rec[j].w;
+        if (len >= 1 && len <= 8) { // still room in the CTA's table?
+            const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
+            const u32 s = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
+            const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[s]), 0ull, k0);
             if (old == 0 || old == k0) {
-                u32 *cell = reinterpret_cast<u32 *>(&tab[slot]);
+                u32 *cell = reinterpret_cast<u32 *>(&tab[s]);
                 atomicAdd(cell + 2, (u32)delta);
-                atomicMin(cell + 3, rec.z);
-            } else {
-                made = word_insert(*Tp, k0, 0ull, delta, Lp->base + end) | (1u << 24);
-            }
-        } else if (len <= 16) {
-            const u64 k1 = load8_unaligned(Lp->buf, end - len + 8, len - 8);
-            made = word_insert(*Tp, k0, k1, delta, Lp->base + end);
-        } else {
-            made = long_insert(Tp, Lp->buf, end - len, len, delta, Lp->base + end) << 16;
+                atomicMin(cell + 3, rec[j].z);
+            } else { todo |= 1u << j; made += 1u << 16; }
+        } else if (len >= 9 && len <= 16) todo |= 1u << j;
+    }
+#pragma unroll
+    for (int j = 0; j < R; j++) { // issue every read
+        const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
+        slot[j] = 0; key[j] = make_ulonglong2(0, 0); k1[j] = 0;
+        if (todo & (1u << j)) {
+            slot[j] = word_home(T, k0, rec[j].w);
+            key[j] = __ldcg(&T.w_keys[slot[j]]);
+            if (rec[j].w > 8) k1[j] = load8_unaligned(Lp->buf, cta_base + rec[j].z - rec[j].w + 8, rec[j].w - 8);
         }
     }
+#pragma unroll
+    for (int j = 0; j < R; j++) { // then use them
+        const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
+        const u64 end = cta_base + rec[j].z; // buffer-relative offset of the delimiter
+        if (todo & (1u << j)) made += word_insert_at(T, k0, k1[j], delta, Lp->base + end, slot[j], key[j]);
+        else if (rec[j].w > 16) made += long_insert(Tp, Lp->buf, end - rec[j].w, rec[j].w, delta, Lp->base + end) << 8;
+    }
     __syncwarp();
-    uint4 mv = make_uint4(0, 0, 0, 0);
-    const bool keep = lane + take < count;
-    if (keep) mv = q[lane + take];
-    __syncwarp();
-    if (keep) q[lane] = mv;
-    __syncwarp();
+    // move what is left to the front of the queue
+    for (u32 base = 0; base + take < count; base += 32) {
+        uint4 mv = make_uint4(0, 0, 0, 0);
+        const bool keep = base + lane + take < count;
+        if (keep) mv = q[base + lane + take];
+        __syncwarp();
+        if (keep) q[base + lane] = mv;
+        __syncwarp();
+    }
     return made;
 }
 
@@ -739,12 +775,12 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                         n_long += defer && len > 8;
                         q_count += __popc(bq);
                         __syncwarp();
-                        if (q_count >= 32) {
+                        if (q_count >= (u32)kDrainBatch) {
 #ifndef WC_EXP_NODRAIN
-                            const u32 made = drain_deferred(dq, q_count, 32, &L, &T, cta_base, tab);
-                            n_wnew += made & 1u; n_xnew += (made >> 16) & 1u; n_spill += made >> 24;
+                            const u32 made = drain_deferred(dq, q_count, kDrainBatch, &L, &T, cta_base, tab);
+                            n_wnew += made & 0xFFu; n_xnew += (made >> 8) & 0xFFu; n_spill += made >> 16;
 #endif
-                            q_count -= 32;
+                            q_count -= kDrainBatch;
                         }
                     }
                 }
@@ -754,9 +790,10 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             // the next tile sees this tile's last delimiter at a negative position
             carry_prev = first_prev - kTile < -(1 << 30) ? -(1 << 30) : first_prev - kTile;
         }
-        if (q_count > 0) {
-            const u32 made = drain_deferred(dq, q_count, q_count, &L, &T, cta_base, tab);
-            n_wnew += made & 1u; n_xnew += (made >> 16) & 1u; n_spill += made >> 24;
+        if (q_count > 0) { // at most kQueue - 1 records: one call takes them all (4 per lane, then the rest)
+            u32 made = drain_deferred(dq, q_count, q_count < (u32)kDrainBatch ? q_count : kDrainBatch, &L, &T, cta_base, tab);
+            if (q_count > (u32)kDrainBatch) made += drain_deferred(dq, q_count - kDrainBatch, q_count - kDrainBatch, &L, &T, cta_base, tab);
+            n_wnew += made & 0xFFu; n_xnew += (made >> 8) & 0xFFu; n_spill += made >> 16;
         }
     }
 
@@ -786,7 +823,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
         const uint4 ent = tab[i];
         if ((ent.x | ent.y) != 0 && ent.z != 0) {
             const u64 key = (u64)ent.x | ((u64)ent.y << 32);
-            n_wnew += word_insert(T, key, 0ull, (u64)(long long)(int)ent.z, L.base + cta_base + ent.w);
+            n_wnew += word_insert(T, key, 0ull, key_len8(key), (u64)(long long)(int)ent.z, L.base + cta_base + ent.w);
         }
     }
     const u32 w_wnew = __reduce_add_sync(0xFFFFFFFFu, n_wnew);
