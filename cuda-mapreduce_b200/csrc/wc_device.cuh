@@ -18,16 +18,23 @@ namespace wc {
 typedef unsigned long long u64;
 typedef unsigned int u32;
 
+#ifndef WC_DRAIN
+#define WC_DRAIN 64
+#endif
+constexpr int kRingBytesC = 2 * 1072, kDlBytesC = 1024, kQueueC = WC_DRAIN + 32;
 constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 B
 constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
-constexpr int kWarps = 16;                 // warps per CTA
+#ifndef WC_WARPS
+#define WC_WARPS 16
+#endif
+constexpr int kWarps = WC_WARPS;           // warps per CTA
 constexpr int kThreads = kWarps * 32;
-constexpr u32 kSmemEntries = 8768;         // 16-byte entries of the per-CTA table (137 KiB)
+constexpr u32 kSmemEntries = ((232448 - 256 - kWarps * (kRingBytesC + kDlBytesC + kQueueC * 16)) / 16) & ~31u; // 16-byte entries of the per-CTA table: whatever the warps leave
 constexpr int kBufBytes = 1072;            // one tile buffer: 16 B tail of the previous tile + tile + slack
 constexpr int kRingBytes = 2 * kBufBytes;  // per warp: two buffers, the next tile lands by cp.async
 constexpr int kDlCap = 512;                // per warp: delimiter list entries
 constexpr int kDlBytes = kDlCap * 2;
-constexpr int kDrainBatch = 128;           // deferred words handled per drain: four per lane
+constexpr int kDrainBatch = WC_DRAIN;      // deferred words handled per drain: WC_DRAIN / 32 per lane
 constexpr int kQueue = kDrainBatch + 32;   // per warp: deferred words (16-byte records)
 constexpr u64 kNone = ~0ull;
 
@@ -36,6 +43,7 @@ constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16;
 constexpr size_t kSmemTotal = kSmemTableBytes + (size_t)kWarps * kWarpSmemBytes;
 static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
 static_assert(kSmemTotal <= 232448 - 64, "more shared memory than an sm_100 CTA can have");
+static_assert(kRingBytesC == kRingBytes && kDlBytesC == kDlBytes && kQueueC == kQueue, "keep the sizing constants in step");
 
 enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u };
 
@@ -602,15 +610,23 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             // ---- classify 2 x 16 bytes
             u32 dmA, dmB, lfA, lfB, liveA, liveB;
             {
-                const FastFlags a0 = classify_fast4(va.x), a1 = classify_fast4(va.y), a2 = classify_fast4(va.z),
-                                a3 = classify_fast4(va.w);
-                const FastFlags b0 = classify_fast4(vb.x), b1 = classify_fast4(vb.y), b2 = classify_fast4(vb.z),
-                                b3 = classify_fast4(vb.w);
-                dmA = movemask16(a0.cand, a1.cand, a2.cand, a3.cand);
-                dmB = movemask16(b0.cand, b1.cand, b2.cand, b3.cand);
-                lfA = movemask16(a0.lf, a1.lf, a2.lf, a3.lf);
-                lfB = movemask16(b0.lf, b1.lf, b2.lf, b3.lf);
-                const u32 ex = a0.ex | a1.ex | a2.ex | a3.ex | b0.ex | b1.ex | b2.ex | b3.ex;
+                // (one sub-tile at a time: keeps the number of live registers down)
+                u32 ex;
+                {
+                    const FastFlags a0 = classify_fast4(va.x), a1 = classify_fast4(va.y), a2 = classify_fast4(va.z),
+                                    a3 = classify_fast4(va.w);
+                    dmA = movemask16(a0.cand, a1.cand, a2.cand, a3.cand);
+                    lfA = movemask16(a0.lf, a1.lf, a2.lf, a3.lf);
+                    ex = a0.ex | a1.ex | a2.ex | a3.ex;
+                }
+                asm volatile("" ::: "memory");
+                {
+                    const FastFlags b0 = classify_fast4(vb.x), b1 = classify_fast4(vb.y), b2 = classify_fast4(vb.z),
+                                    b3 = classify_fast4(vb.w);
+                    dmB = movemask16(b0.cand, b1.cand, b2.cand, b3.cand);
+                    lfB = movemask16(b0.lf, b1.lf, b2.lf, b3.lf);
+                    ex |= b0.ex | b1.ex | b2.ex | b3.ex;
+                }
                 liveA = dmA; liveB = dmB;
                 if (__any_sync(0xFFFFFFFFu, ex != 0) || killed) {
                     acc_slow += lane == 0;
@@ -694,33 +710,17 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                 if (!dense || ph == 0) {
                     u32 m = dmA;
                     unsigned short *o = dl + exclA;
-                    const u32 basepos = lane * 16;
-#pragma unroll
-                    for (int i = 0; i < 4; i++) { // most lanes hold at most 4 delimiters
-                        const u32 p = __ffs(m) - 1;
-                        if (m) o[i] = (unsigned short)((basepos + p) | (((liveA >> p) & 1u) << 15));
-                        m &= m - 1;
-                    }
-                    o += 4;
                     while (m) {
                         const u32 p = __ffs(m) - 1; m &= m - 1;
-                        *o++ = (unsigned short)((basepos + p) | (((liveA >> p) & 1u) << 15));
+                        *o++ = (unsigned short)((lane * 16 + p) | (((liveA >> p) & 1u) << 15));
                     }
                 }
                 if (!dense || ph == 1) {
                     u32 m = dmB;
                     unsigned short *o = dl + (dense ? 0u : totA) + exclB;
-                    const u32 basepos = kSub + lane * 16;
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const u32 p = __ffs(m) - 1;
-                        if (m) o[i] = (unsigned short)((basepos + p) | (((liveB >> p) & 1u) << 15));
-                        m &= m - 1;
-                    }
-                    o += 4;
                     while (m) {
                         const u32 p = __ffs(m) - 1; m &= m - 1;
-                        *o++ = (unsigned short)((basepos + p) | (((liveB >> p) & 1u) << 15));
+                        *o++ = (unsigned short)((kSub + lane * 16 + p) | (((liveB >> p) & 1u) << 15));
                     }
                 }
                 __syncwarp();
