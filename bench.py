@@ -109,14 +109,6 @@ def workload_params(name, n_gpus):
     raise SystemExit("unknown workload " + name)
 
 
-def shard_range(total, block, rank, world):
-    """Block-aligned [lo, hi) of this rank's shard (blocks end with a newline: shard edges are line starts)."""
-    nblocks = (total + block - 1) // block
-    b0 = nblocks * rank // world
-    b1 = nblocks * (rank + 1) // world
-    return b0 * block, min(b1 * block, total)
-
-
 def run_reference(args):
     """--impl reference: the reference semantics on host cores (oracle port, all threads)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -179,6 +171,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
     pkg = load_pkg()
+    from cuda_mapreduce_b200 import multi
+    shard_range = multi.shard_range
     wp = workload_params(args.workload, world)
 
     # ---- this rank's shard of the synthetic corpus, generated into pinned host memory
@@ -198,9 +192,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    devt = torch.device("cuda", local_rank)
+
     def step_device():
         eng.reset()
-        eng.count_device(dev.data_ptr(), nbytes, last_piece=True)
+        eng.count_device(dev.data_ptr(), nbytes, last_piece=(rank == world - 1))
+        if world > 1:  # key-owner exchange: NCCL all-to-all, owner reduce, gather on rank 0
+            with torch.cuda.stream(ext):
+                multi.exchange_and_gather(eng, devt)
 
     # ---- value: device-resident, CUDA events on the launching stream
     for _ in range(args.warmup):
@@ -232,7 +231,10 @@ def main():
     kernel_ms = ksum / args.steps
     clocks = sampler.stop() if rank == 0 else None
 
-    res = eng.finish(keep_rows=False)
+    if world > 1:
+        eng.reset()
+        eng.count_device(dev.data_ptr(), nbytes, last_piece=(rank == world - 1))
+    res = eng.finish(keep_rows=False)  # this rank's shard alone: its words for the words/s figure
     words = res.stats["n_flush"]
 
     t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
@@ -248,6 +250,12 @@ def main():
     def step_e2e():
         eng.reset()
         eng.feed((host.data_ptr(), nbytes))
+        if world > 1:
+            with torch.cuda.stream(ext):
+                _, is_root = multi.exchange_and_gather(eng, devt)
+            if not is_root:
+                eng.sync()
+                return None
         return eng.finish(keep_rows=False)
 
     e2e_steps = 0 if args.no_e2e else max(3, args.steps // 2)
@@ -277,7 +285,8 @@ def main():
                    "distinct_words": res.stats["n_distinct"], "deferred_1to8B_words": res.stats["n_spilled"],
                    "words_9B_plus": res.stats["n_long_words"],
                    "l2": "input (1e9 B) is larger than the 126 MB L2, every step re-reads it from HBM",
-                   "step": "wc_reset (table memset) + tokenize/count kernel + roll-back/summary kernel",
+                   "step": "wc_reset (table memset) + tokenize/count kernel + roll-back/summary kernel"
+                           + (" + key-owner exchange (NCCL all-to-all, owner reduce, gather on rank 0)" if world > 1 else ""),
                    "vocab_seed": corpus.vocab_seed, "text_seed": corpus.text_seed},
         "words_per_s": all_words / (ms_step * 1e-3),
         "frac_of_hbm_nominal_8TBs": value / world / 8000.0,

@@ -13,6 +13,7 @@
 
 #include "../../include/wc.h"
 #include "wc_device.cuh"
+#include "wc_shuffle.cuh"
 #include "wc_finalize.h"
 
 using wc::u32;
@@ -42,6 +43,10 @@ struct wc_engine {
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_counted[2] = {nullptr, nullptr};
     int ring = 0;
     std::vector<uint8_t> carry; // bytes after the last '\n' seen so far (an unfinished line)
+
+    u64 *d_cursors = nullptr;   // shuffle: per-partition counts / cursors (2 * kMaxParts + 2 words)
+    bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
+    u64 job_bytes = 0;
 
     u64 consumed = 0; // bytes handed to the device so far
     u64 fed = 0;      // bytes given to wc_feed / wc_count_device
@@ -138,6 +143,7 @@ void wc_destroy(wc_engine *e) {
     if (e->T.arena) cudaFree(e->T.arena);
     if (e->d_status) cudaFree(e->d_status);
     if (e->d_ws) cudaFree(e->d_ws);
+    if (e->d_cursors) cudaFree(e->d_cursors);
     if (e->h_status) cudaFreeHost(e->h_status);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
@@ -207,6 +213,7 @@ int wc_reset(wc_engine *e) {
     int rc = reset_device_state(e);
     if (rc != WC_OK) return rc;
     e->carry.clear();
+    e->job_stats_set = false; e->job_bytes = 0;
     e->consumed = 0; e->fed = 0; e->launches = 0; e->device_ms = 0; e->count_kernel_ms = 0;
     for (auto &p : e->ev_used) { e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.mid); e->ev_pool.push_back(p.b); }
     e->ev_used.clear();
@@ -427,7 +434,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
 
     wc_result *r = new (std::nothrow) wc_result();
     if (!r) return WC_ERR_NOMEM;
-    const u64 total_bytes = e->consumed;
+    const u64 total_bytes = e->job_stats_set ? e->job_bytes : e->consumed;
     const u64 stop_abs = st.stop == wc::kNone ? e->cfg.base_offset + total_bytes : st.stop;
     u64 lost = st.lost_empty;
     if (!st.p0_found || st.p0 >= stop_abs) lost = st.n_empty; // no non-empty word at all: every empty one is lost
@@ -469,6 +476,168 @@ extern "C" uint32_t wc_debug_smem_entries(void) { return wc::kSmemEntries; }
 extern "C" uint32_t wc_debug_smem_slot(uint64_t key) {
     return (uint32_t)(((uint64_t)wc::hash32((u32)key, (u32)(key >> 32)) * wc::kSmemEntries) >> 32);
 }
+
+
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU: shard counters and the key-owner exchange.  One engine per GPU counts
+// its byte range (wc_config.base_offset = where the range starts); the caller moves the exported
+// buffers between GPUs (NCCL all-to-all / gather through torch.distributed or any other transport).
+
+namespace { constexpr u32 kMaxParts = 64; }
+
+static int ensure_cursors(wc_engine *e) {
+    if (!e->d_cursors) CK(cudaMalloc((void **)&e->d_cursors, (2 * kMaxParts + 2) * sizeof(u64)));
+    return WC_OK;
+}
+
+extern "C" {
+
+int wc_shard_stats_get(wc_engine *e, wc_shard_stats *out) {
+    if (!e || !out) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    if (!e->carry.empty()) { e->err = "wc_shard_stats_get before the input is complete (unfinished line)"; return WC_ERR_INVALID; }
+    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+    int rc = wc_sync(e);
+    if (rc != WC_OK) return rc;
+    const wc::Status st = *e->h_status;
+    if (st.err) { e->err = "device tables full"; return WC_ERR_TABLE_FULL; }
+    memset(out, 0, sizeof(*out));
+    out->base = e->cfg.base_offset; out->bytes = e->consumed;
+    out->n_flush = st.n_flush; out->n_empty = st.n_empty; out->lost_empty = st.lost_empty;
+    out->p0 = st.p0; out->p0_found = st.p0_found;
+    out->stop = st.stop; // absolute, ~0 if this shard saw no reason to stop
+    return WC_OK;
+}
+
+// Pure host logic: what the counters of the whole job are, given every shard's (in input order).
+// A shard at or after the first STOP contributes nothing (main.cu:185: the reference stops reading);
+// the shard holding STOP has already rolled its own tail back.  Empty words count as lost until the
+// first non-empty word of the whole job (main.cu:81,103).
+int wc_shard_stats_reduce(const wc_shard_stats *s, size_t n, wc_shard_stats *out) {
+    if (!s || !out || n == 0) return WC_ERR_INVALID;
+    for (size_t i = 1; i < n; i++)
+        if (s[i].base != s[i - 1].base + s[i - 1].bytes) return WC_ERR_INVALID; // shards must tile the input
+    wc_shard_stats j;
+    memset(&j, 0, sizeof(j));
+    j.base = s[0].base; j.stop = ~0ull; j.p0 = ~0ull;
+    for (size_t i = 0; i < n; i++) {
+        j.bytes += s[i].bytes;
+        if (j.stop != ~0ull) continue; // after STOP: ignored
+        j.n_flush += s[i].n_flush; j.n_empty += s[i].n_empty;
+        if (!j.p0_found) {
+            if (s[i].p0_found && s[i].p0 < s[i].stop) { j.p0_found = 1; j.p0 = s[i].p0; j.lost_empty += s[i].lost_empty; }
+            else j.lost_empty += s[i].n_empty;
+        }
+        if (s[i].stop != ~0ull) j.stop = s[i].stop;
+    }
+    *out = j;
+    return WC_OK;
+}
+
+int wc_shard_stats_set(wc_engine *e, const wc_shard_stats *job) {
+    if (!e || !job) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    wc::Status st = *e->h_status;
+    st.n_flush = job->n_flush; st.n_empty = job->n_empty; st.lost_empty = job->lost_empty;
+    st.p0 = job->p0; st.p0_found = job->p0_found; st.stop = job->stop;
+    *e->h_status = st;
+    CK(cudaMemcpyAsync(e->d_status, e->h_status, sizeof(st), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->job_stats_set = true; e->job_bytes = job->bytes;
+    return WC_OK;
+}
+
+int wc_clear_tables(wc_engine *e) {
+    if (!e) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaMemsetAsync(e->table_block, 0, e->table_block_bytes, e->stream));
+    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->h_status->w_entries = 0; e->h_status->x_entries = 0; e->h_status->arena_used = 1;
+    CK(cudaMemcpyAsync(e->d_status, e->h_status, sizeof(wc::Status), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return WC_OK;
+}
+
+int wc_export_counts(wc_engine *e, uint32_t n_parts, uint64_t *word_counts, uint64_t *long_entries,
+                     uint64_t *long_blob_bytes) {
+    if (!e || !word_counts || n_parts == 0 || n_parts > kMaxParts) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    int rc = ensure_cursors(e);
+    if (rc != WC_OK) return rc;
+    CK(cudaMemsetAsync(e->d_cursors, 0, (2 * kMaxParts + 2) * sizeof(u64), e->stream));
+    wc::export_count_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, n_parts, e->d_cursors);
+    wc::count_long_kernel<<<e->num_sms, 256, 0, e->stream>>>(e->T, e->d_cursors + 2 * kMaxParts);
+    CK(cudaGetLastError());
+    u64 host[2 * kMaxParts + 2];
+    CK(cudaMemcpyAsync(host, e->d_cursors, sizeof(host), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    for (u32 p = 0; p < n_parts; p++) word_counts[p] = host[p];
+    if (long_entries) *long_entries = host[2 * kMaxParts];
+    if (long_blob_bytes) *long_blob_bytes = host[2 * kMaxParts + 1];
+    e->launches += 2;
+    return WC_OK;
+}
+
+int wc_export_words(wc_engine *e, uint32_t n_parts, const uint64_t *part_offsets, void *dev_records) {
+    if (!e || !part_offsets || !dev_records || n_parts == 0 || n_parts > kMaxParts) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    int rc = ensure_cursors(e);
+    if (rc != WC_OK) return rc;
+    u64 host[2 * kMaxParts];
+    memset(host, 0, sizeof(host));
+    for (u32 p = 0; p < n_parts; p++) host[p] = part_offsets[p]; // [0, kMaxParts): offsets, [kMaxParts, ..): cursors
+    CK(cudaMemcpyAsync(e->d_cursors, host, sizeof(host), cudaMemcpyHostToDevice, e->stream));
+    wc::export_scatter_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, n_parts, e->d_cursors, e->d_cursors + kMaxParts,
+                                                                    (wc::WordRecord *)dev_records);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(e->stream)); // `host` is on this stack frame
+    e->launches += 1;
+    return WC_OK;
+}
+
+int wc_export_long(wc_engine *e, void *dev_meta, void *dev_blob) {
+    if (!e || !dev_meta || !dev_blob) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    int rc = ensure_cursors(e);
+    if (rc != WC_OK) return rc;
+    CK(cudaMemsetAsync(e->d_cursors + 2 * kMaxParts, 0, 2 * sizeof(u64), e->stream));
+    wc::export_long_kernel<<<e->num_sms, 256, 0, e->stream>>>(e->T, e->d_cursors + 2 * kMaxParts, (wc::LongRecord *)dev_meta,
+                                                             (u64 *)dev_blob);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(e->stream));
+    e->launches += 1;
+    return WC_OK;
+}
+
+int wc_import_words(wc_engine *e, const void *dev_records, uint64_t n_records) {
+    if (!e || (!dev_records && n_records)) return WC_ERR_INVALID;
+    if (n_records == 0) return WC_OK;
+    CK(cudaSetDevice(e->device));
+    wc::import_words_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, (const wc::WordRecord *)dev_records, n_records);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(e->stream));
+    e->launches += 1;
+    return WC_OK;
+}
+
+int wc_import_long(wc_engine *e, const void *dev_meta, uint64_t n_entries, const void *dev_blob) {
+    if (!e || ((!dev_meta || !dev_blob) && n_entries)) return WC_ERR_INVALID;
+    if (n_entries == 0) return WC_OK;
+    CK(cudaSetDevice(e->device));
+    wc::import_long_kernel<<<e->num_sms, 256, 0, e->stream>>>(e->T, (const wc::LongRecord *)dev_meta, n_entries,
+                                                             (const uint8_t *)dev_blob);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(e->stream));
+    e->launches += 1;
+    return WC_OK;
+}
+
+uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts) { return wc::key_owner(k0, k1, n_parts); }
+
+} // extern "C"
 
 // ------------------------------------------------------------------------------------------------
 // wc_count_device_static: the count kernel for callers that must not allocate.

@@ -46,6 +46,12 @@ class Stats(C.Structure):
     ]
 
 
+class ShardStats(C.Structure):
+    _fields_ = [("base", C.c_uint64), ("bytes", C.c_uint64), ("n_flush", C.c_uint64), ("n_empty", C.c_uint64),
+                ("lost_empty", C.c_uint64), ("p0", C.c_uint64), ("stop", C.c_uint64), ("p0_found", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+
 class WcError(RuntimeError):
     def __init__(self, code, text):
         super().__init__("libwc: %s (%d): %s" % (lib().wc_strerror(code).decode(), code, text))
@@ -101,6 +107,17 @@ def lib():
     L.wc_debug_classify16.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.wc_debug_smem_slot.argtypes = [u64]
     L.wc_debug_smem_slot.restype = C.c_uint32
+    L.wc_shard_stats_get.argtypes = [vp, C.POINTER(ShardStats)]
+    L.wc_shard_stats_reduce.argtypes = [C.POINTER(ShardStats), sz, C.POINTER(ShardStats)]
+    L.wc_shard_stats_set.argtypes = [vp, C.POINTER(ShardStats)]
+    L.wc_clear_tables.argtypes = [vp]
+    L.wc_export_counts.argtypes = [vp, C.c_uint32, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+    L.wc_export_words.argtypes = [vp, C.c_uint32, C.POINTER(u64), vp]
+    L.wc_export_long.argtypes = [vp, vp, vp]
+    L.wc_import_words.argtypes = [vp, vp, u64]
+    L.wc_import_long.argtypes = [vp, vp, u64, vp]
+    L.wc_key_owner.argtypes = [u64, u64, C.c_uint32]
+    L.wc_key_owner.restype = C.c_uint32
     L.wc_count_device_static.argtypes = [C.c_int, vp, sz, vp, C.c_uint32, vp, C.c_uint32, vp, u64, vp, vp]
     L.wc_static_last_error.restype = C.c_char_p
     L.runMapReduce.argtypes = [vp, C.c_int, vp, C.POINTER(C.c_int)]
@@ -198,6 +215,37 @@ class Engine:
         r = C.c_void_p()
         self._ck(lib().wc_finish(self.h, C.byref(r)))
         return Result(r, keep_rows)
+
+    # ---- multi-GPU protocol (include/wc.h)
+    def shard_stats(self):
+        st = ShardStats()
+        self._ck(lib().wc_shard_stats_get(self.h, C.byref(st)))
+        return st
+
+    def set_job_stats(self, job):
+        self._ck(lib().wc_shard_stats_set(self.h, C.byref(job)))
+
+    def clear_tables(self):
+        self._ck(lib().wc_clear_tables(self.h))
+
+    def export_counts(self, n_parts):
+        counts = (C.c_uint64 * n_parts)()
+        nl, lb = C.c_uint64(), C.c_uint64()
+        self._ck(lib().wc_export_counts(self.h, n_parts, counts, C.byref(nl), C.byref(lb)))
+        return list(counts), nl.value, lb.value
+
+    def export_words(self, n_parts, offsets, dev_ptr):
+        offs = (C.c_uint64 * n_parts)(*offsets)
+        self._ck(lib().wc_export_words(self.h, n_parts, offs, C.c_void_p(dev_ptr)))
+
+    def export_long(self, dev_meta, dev_blob):
+        self._ck(lib().wc_export_long(self.h, C.c_void_p(dev_meta), C.c_void_p(dev_blob)))
+
+    def import_words(self, dev_ptr, n):
+        self._ck(lib().wc_import_words(self.h, C.c_void_p(dev_ptr), n))
+
+    def import_long(self, dev_meta, n, dev_blob):
+        self._ck(lib().wc_import_long(self.h, C.c_void_p(dev_meta), n, C.c_void_p(dev_blob)))
 
     def device_ms(self):
         ms, kms, n = C.c_double(), C.c_double(), C.c_uint64()

@@ -143,6 +143,42 @@ WC_API int wc_device_ms(wc_engine *e, double *ms, double *count_kernel_ms, uint6
  * bracket work with their own events. */
 WC_API void *wc_stream(wc_engine *e);
 
+/* ---- multi-GPU: byte-range shards + key-owner exchange ---------------------------
+ *
+ * Nothing to replace in the reference: it drives one GPU (main.cu:133-162).  One engine per GPU counts
+ * one byte range of the input (ranges are cut at line starts; wc_config.base_offset = where the range
+ * begins, so that first-occurrence offsets stay global).  Afterwards:
+ *   1. wc_shard_stats_get on every engine; wc_shard_stats_reduce over all of them (any host);
+ *      an engine whose range begins at or after the job's STOP calls wc_clear_tables.
+ *   2. wc_export_counts / wc_export_words: the word table as 32-byte records {key0, key1, count,
+ *      first} grouped by owner = wc_key_owner(key, n_parts); the caller runs the all-to-all (NCCL).
+ *   3. every engine: wc_clear_tables, then wc_import_words of what it received -> each distinct word
+ *      is reduced on exactly one GPU.
+ *   4. gather: owners export again (n_parts = 1) and the gathering engine imports; words of 17+ bytes
+ *      travel once, as wc_export_long / wc_import_long.
+ *   5. wc_shard_stats_set(job counters) + wc_finish on the gathering engine.
+ * The transport is the caller's: bench.py uses torch.distributed (NCCL over NVLink). */
+typedef struct wc_shard_stats {
+    uint64_t base, bytes;      /* the shard: [base, base + bytes) of the input */
+    uint64_t n_flush, n_empty, lost_empty;
+    uint64_t p0;               /* offset that flushed the shard's first non-empty word (if p0_found) */
+    uint64_t stop;             /* absolute STOP offset seen in this shard, ~0 if none */
+    uint32_t p0_found, reserved;
+} wc_shard_stats;
+#define WC_WORD_RECORD_BYTES 32
+#define WC_LONG_RECORD_BYTES 32
+WC_API int wc_shard_stats_get(wc_engine *e, wc_shard_stats *out);
+WC_API int wc_shard_stats_reduce(const wc_shard_stats *shards, size_t n, wc_shard_stats *job);
+WC_API int wc_shard_stats_set(wc_engine *e, const wc_shard_stats *job);
+WC_API int wc_clear_tables(wc_engine *e);
+WC_API int wc_export_counts(wc_engine *e, uint32_t n_parts, uint64_t *word_counts, uint64_t *long_entries,
+                            uint64_t *long_blob_bytes);
+WC_API int wc_export_words(wc_engine *e, uint32_t n_parts, const uint64_t *part_offsets, void *dev_records);
+WC_API int wc_export_long(wc_engine *e, void *dev_meta, void *dev_blob);
+WC_API int wc_import_words(wc_engine *e, const void *dev_records, uint64_t n_records);
+WC_API int wc_import_long(wc_engine *e, const void *dev_meta, uint64_t n_entries, const void *dev_blob);
+WC_API uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts);
+
 /* ---- wc_count_device_static: counting without any allocation -------------------------------
  *
  * No counterpart in the reference (whose runMapReduce cudaMallocs and cudaFrees on every call,

@@ -294,3 +294,67 @@ def test_config2_full_size_1GB(pkg):
         assert got2.pairs() == got.pairs() and got2.total == got.total
     exp = O.fast_mt(host.numpy())
     assert got.pairs() == exp.pairs() and got.total == exp.total and got.stats["n_flush"] == exp.n_flush
+
+
+def test_key_owner_exchange_two_engines_one_gpu(pkg):
+    """The multi-GPU protocol (include/wc.h) with its real export / import kernels:
+    two engines on this one GPU stand for two ranks, device-to-device copies for the NCCL all-to-all."""
+    import torch
+    from cuda_mapreduce_b200 import multi
+    rng = random.Random(12)
+    body = random_text(rng, 120000, weird=0.0).replace(b"\n\n", b"\n")
+    long_words = b" ".join(bytes(rng.choice(b"abcdefgh") for _ in range(rng.randint(17, 60))) for _ in range(50))
+    texts = [
+        body + b" " + long_words + b"\n" + body[:3000],
+        b"  \n \n" + body[:50000] + long_words + b"\n",
+        body[:40000] + b"\n\n" + body[40000:],          # STOP inside the first shard
+    ]
+    world, REC = 2, 32
+    for data in texts:
+        cuts = multi.line_aligned_cuts(data, world)
+        engs = [pkg.Engine(base_offset=cuts[r], chunk_bytes=1 << 20, **SMALL) for r in range(world)]
+        try:
+            for r, e in enumerate(engs):
+                e.feed(data[cuts[r]:cuts[r + 1]])
+            stats = [e.shard_stats() for e in engs]
+            job = multi.reduce_stats(stats)
+            for st, e in zip(stats, engs):
+                if job.stop != multi.NONE and st.base >= job.stop and st.bytes > 0:
+                    e.clear_tables()
+            sends, counts, longs = [], [], []
+            for e in engs:
+                c, n_long, lb = e.export_counts(world)
+                meta = torch.zeros(max(n_long * REC, 1), dtype=torch.uint8, device="cuda")
+                blob = torch.zeros(max(lb, 8), dtype=torch.uint8, device="cuda")
+                if n_long:
+                    e.export_long(meta.data_ptr(), blob.data_ptr())
+                longs.append((meta, n_long, blob))
+                offs = [0, c[0]]
+                buf = torch.zeros(max(sum(c) * REC, 1), dtype=torch.uint8, device="cuda")
+                if sum(c):
+                    e.export_words(world, offs, buf.data_ptr())
+                sends.append(buf); counts.append(c)
+            for dst, e in enumerate(engs):                      # "all-to-all"
+                e.clear_tables()
+                for src in range(world):
+                    off = sum(counts[src][:dst]) * REC
+                    part = sends[src][off:off + counts[src][dst] * REC].clone()
+                    e.import_words(part.data_ptr(), counts[src][dst])
+            root = engs[0]                                     # gather on rank 0
+            c1, _, _ = engs[1].export_counts(1)
+            buf = torch.zeros(max(c1[0] * REC, 1), dtype=torch.uint8, device="cuda")
+            if c1[0]:
+                engs[1].export_words(1, [0], buf.data_ptr())
+            root.import_words(buf.data_ptr(), c1[0])
+            for meta, n_long, blob in longs:
+                root.import_long(meta.data_ptr(), n_long, blob.data_ptr())
+            root.set_job_stats(job)
+            got = root.finish()
+        finally:
+            for e in engs:
+                e.close()
+        exp = O.fast(data)
+        assert got.pairs() == exp.pairs() and got.total == exp.total
+        assert got.firsts == [f for _, _, f in exp.rows]
+        assert (got.stats["n_flush"], got.stats["n_empty"], got.stats["n_lost_empty"], got.stats["stop"]) == \
+               (exp.n_flush, exp.n_empty, exp.n_lost_empty, exp.stop)
