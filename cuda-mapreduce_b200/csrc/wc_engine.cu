@@ -378,15 +378,25 @@ int wc_host_alloc(void **p, size_t n) {
 
 int wc_host_free(void *p) { return cudaFreeHost(p) == cudaSuccess ? WC_OK : WC_ERR_CUDA; }
 
+int wc_end_input(wc_engine *e) {
+    if (!e) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    if (!e->carry.empty()) { // the unterminated end of the input (main.cu:198-203 drops its last word)
+        int rc = feed_piece(e, e->carry.data(), e->carry.size(), 1);
+        if (rc != WC_OK) return rc;
+        CK(cudaStreamSynchronize(e->copy_stream));
+        CK(cudaStreamSynchronize(e->stream));
+        e->carry.clear();
+    }
+    return WC_OK;
+}
+
 int wc_finish(wc_engine *e, wc_result **out) {
     if (!e || !out) return WC_ERR_INVALID;
     *out = nullptr;
     CK(cudaSetDevice(e->device));
-    int rc;
-    if (!e->carry.empty()) { // the unterminated end of the input (main.cu:198-203 drops its last word)
-        rc = feed_piece(e, e->carry.data(), e->carry.size(), 1);
-        if (rc != WC_OK) return rc;
-    }
+    int rc = wc_end_input(e);
+    if (rc != WC_OK) return rc;
     CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
     rc = wc_sync(e);
     if (rc != WC_OK) return rc;
@@ -495,7 +505,7 @@ extern "C" {
 int wc_shard_stats_get(wc_engine *e, wc_shard_stats *out) {
     if (!e || !out) return WC_ERR_INVALID;
     CK(cudaSetDevice(e->device));
-    if (!e->carry.empty()) { e->err = "wc_shard_stats_get before the input is complete (unfinished line)"; return WC_ERR_INVALID; }
+    { int rc0 = wc_end_input(e); if (rc0 != WC_OK) return rc0; } // a shard's counters describe all of its bytes
     CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
     int rc = wc_sync(e);
     if (rc != WC_OK) return rc;

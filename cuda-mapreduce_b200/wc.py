@@ -80,6 +80,7 @@ def lib():
     L.wc_feed.argtypes = [vp, vp, sz]
     L.wc_count_device.argtypes = [vp, vp, sz, C.c_int]
     L.wc_sync.argtypes = [vp]
+    L.wc_end_input.argtypes = [vp]
     L.wc_finish.argtypes = [vp, C.POINTER(vp)]
     L.wc_result_rows.argtypes = [vp]
     L.wc_result_rows.restype = sz

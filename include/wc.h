@@ -108,6 +108,10 @@ WC_API int wc_feed(wc_engine *e, const void *bytes, size_t n);
  * buffer must stay valid until wc_sync()/wc_finish(). */
 WC_API int wc_count_device(wc_engine *e, const void *dev_bytes, size_t n, int last_piece);
 
+/* No more input will come: counts the unterminated last line, if any (its final word is dropped
+ * like in main.cu:198-203).  wc_finish and wc_shard_stats_get call it themselves. */
+WC_API int wc_end_input(wc_engine *e);
+
 /* Wait for everything queued so far. */
 WC_API int wc_sync(wc_engine *e);
 
