@@ -18,34 +18,40 @@ namespace wc {
 typedef unsigned long long u64;
 typedef unsigned int u32;
 
-#ifndef WC_DRAIN
-#define WC_DRAIN 64
-#endif
-constexpr int kRingBytesC = 2 * 1072, kDlBytesC = 1024, kQueueC = WC_DRAIN + 32;
-constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 B
-constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 #ifndef WC_WARPS
 #define WC_WARPS 16
 #endif
+#ifndef WC_CONSUMERS
+#define WC_CONSUMERS 2
+#endif
+#ifndef WC_DRAIN
+#define WC_DRAIN 64
+#endif
+constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 B
+constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = WC_WARPS;           // warps per CTA
+constexpr int kConsumers = WC_CONSUMERS;   // of which only insert deferred words into the global tables
+constexpr int kProducers = kWarps - kConsumers; // the others tokenize and count; the text is split over these
 constexpr int kThreads = kWarps * 32;
-constexpr u32 kSmemEntries = ((232448 - 256 - kWarps * (kRingBytesC + kDlBytesC + kQueueC * 16)) / 16) & ~31u; // 16-byte entries of the per-CTA table: whatever the warps leave
 constexpr int kBufBytes = 1072;            // one tile buffer: 16 B tail of the previous tile + tile + slack
-constexpr int kRingBytes = 2 * kBufBytes;  // per warp: two buffers, the next tile lands by cp.async
-constexpr int kDlCap = 512;                // per warp: delimiter list entries
+constexpr int kRingBytes = 2 * kBufBytes;  // per producer warp: two buffers, the next tile lands by cp.async
+constexpr int kDlCap = 512;                // per producer warp: delimiter list entries
 constexpr int kDlBytes = kDlCap * 2;
-constexpr int kDrainBatch = WC_DRAIN;      // deferred words handled per drain: WC_DRAIN / 32 per lane
-constexpr int kQueue = kDrainBatch + 32;   // per warp: deferred words (16-byte records)
+constexpr int kDrainBatch = WC_DRAIN;      // deferred words a consumer warp takes at a time (WC_DRAIN / 32 per lane)
+constexpr u32 kDefRing = 1024;             // per CTA: ring of deferred-word records (16 bytes each)
 constexpr u64 kNone = ~0ull;
 
-constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kQueue * 16;
-constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16;
-constexpr size_t kSmemTotal = kSmemTableBytes + (size_t)kWarps * kWarpSmemBytes;
+constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes;
+constexpr size_t kDefRingBytes = (size_t)kDefRing * 16;
+constexpr u32 kSmemEntries = (u32)((232448 - 256 - kDefRingBytes - kProducers * kWarpSmemBytes) / 16) & ~31u;
+constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16; // the per-CTA table gets what is left
+constexpr size_t kSmemTotal = kSmemTableBytes + kDefRingBytes + (size_t)kProducers * kWarpSmemBytes;
 static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
 static_assert(kSmemTotal <= 232448 - 64, "more shared memory than an sm_100 CTA can have");
-static_assert(kRingBytesC == kRingBytes && kDlBytesC == kDlBytes && kQueueC == kQueue, "keep the sizing constants in step");
+static_assert(kConsumers >= 1 && kProducers >= 1 && kDrainBatch % 32 == 0 && kDrainBatch <= 128, "bad build knobs");
+static_assert((kDefRing & (kDefRing - 1)) == 0 && kDefRing >= 4 * kDrainBatch, "ring size");
 
-enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u };
+enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u, kErrRingTimeout = 16u };
 
 // Device-resident job state (one per engine).
 struct Status {
@@ -413,73 +419,110 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
 }
 
 // Deferred words: words of 1..8 bytes that missed in the CTA's table, and every word of 9+ bytes.
-// A record is (first 8 bytes, end offset relative to the CTA's range, length).  They are handled
-// kDrainBatch at a time, away from the hot loop, four per lane, and every global-memory read of the
-// batch is issued before the first one is used, so that the warp waits for one round trip, not for
-// one per word:
+// The warps that tokenize (producers) only append a 16-byte record (first 8 bytes, end offset
+// relative to the CTA's range, length) to a ring in shared memory; the CTA's consumer warps take the
+// records out and do the slow part, so that no tokenizing warp ever waits for global memory:
 //   1..8 bytes  : claim the word's shared-memory slot if it is still free (this is how the CTA's
 //                 table fills up), else count it in the global word table;
 //   9..16 bytes : fetch bytes 8..15 from the text, count in the global word table;
 //   17+ bytes   : the arena-backed long table.
-// Returns new word-table slots | new long-table slots << 8 | short words sent to the global table << 16.
-__device__ __noinline__ u32 drain_deferred(uint4 *q, u32 count, u32 take, const Launch *Lp, const Tables *Tp,
-                                           u64 cta_base, uint4 *tab) {
+// Ring protocol: producers reserve positions with one atomicAdd on `tail` per warp and round, wait
+// until the position's previous occupant has been taken (record.w == 0) and store the record with a
+// single 16-byte store; record.w (the length, never 0) doubles as the "published" flag.  A consumer
+// warp reserves kDrainBatch positions with an atomicAdd on `head`, waits until they are published (or
+// until every producer has finished and the position is past `tail`), copies the records out and
+// zeroes them.  The oldest unconsumed position can always be written, so nobody waits in a circle.
+struct DefCtl { u32 tail, head, done, abort_flag; };
+
+__device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint4 lds128_volatile(const void *p) { // one 16-byte shared-memory read, never cached in registers
+    uint4 v;
+    asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_addr(p)) : "memory");
+    return v;
+}
+
+__device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *Tp,
+                                              u64 cta_base, uint4 *tab) {
     const u32 lane = lane_id();
     const Tables &T = *Tp;
     const u64 delta = Lp->negate ? ~0ull : 1ull;
     constexpr int R = kDrainBatch / 32;
-    uint4 rec[R];
-    u32 slot[R];
-    ulonglong2 key[R];
-    u64 k1[R];
-    u32 todo = 0; // bit j: record j goes to the global word table
-    u32 made = 0;
+    u32 n_wnew = 0, n_xnew = 0, n_spill = 0;
+    volatile DefCtl *vc = ctl;
+    for (;;) {
+        u32 b = 0;
+        if (lane == 0) b = atomicAdd(&ctl->head, (u32)kDrainBatch);
+        b = __shfl_sync(0xFFFFFFFFu, b, 0);
+        uint4 rec[R];
+        u32 live = 0; // bit j: record j was taken
+        u32 spins = 0;
+        bool finished = false;
+        for (;;) { // wait for the batch
+            const bool all_done = vc->done == (u32)kProducers; // read before tail: tail is final once this holds
+            const u32 tail = vc->tail;
+            bool ok = true;
 #pragma unroll
-    for (int j = 0; j < R; j++) {
-        rec[j] = lane + 32 * j < take ? q[lane + 32 * j] : make_uint4(0, 0, 0, 0);
-        const u32 len = rec[j].w;
-        if (len >= 1 && len <= 8) { // still room in the CTA's table?
-            const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-            const u32 s = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
-            const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[s]), 0ull, k0);
-            if (old == 0 || old == k0) {
-                u32 *cell = reinterpret_cast<u32 *>(&tab[s]);
-                atomicAdd(cell + 2, (u32)delta);
-                atomicMin(cell + 3, rec[j].z);
-            } else { todo |= 1u << j; made += 1u << 16; }
-        } else if (len >= 9 && len <= 16) todo |= 1u << j;
-    }
-#pragma unroll
-    for (int j = 0; j < R; j++) { // issue every read
-        const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-        slot[j] = 0; key[j] = make_ulonglong2(0, 0); k1[j] = 0;
-        if (todo & (1u << j)) {
-            slot[j] = word_home(T, k0, rec[j].w);
-            key[j] = __ldcg(&T.w_keys[slot[j]]);
-            if (rec[j].w > 8) k1[j] = load8_unaligned(Lp->buf, cta_base + rec[j].z - rec[j].w + 8, rec[j].w - 8);
+            for (int j = 0; j < R; j++) {
+                if (live & (1u << j)) continue;
+                const u32 pos = b + lane + 32 * j;
+                const uint4 r = lds128_volatile(&ring[pos & (kDefRing - 1)]);
+                if (r.w != 0) {
+                    rec[j] = r; live |= 1u << j;
+                    ring[pos & (kDefRing - 1)].w = 0; // the position may be reused
+                } else if (!(all_done && (int)(tail - pos) <= 0)) ok = false; // reserved but not yet written
+            }
+            if (__all_sync(0xFFFFFFFFu, ok)) { finished = all_done && (int)(tail - b) <= 0; break; }
+            if (++spins > (1u << 22)) { ctl->abort_flag = 1; atomicOr(&T.st->err, kErrRingTimeout); break; }
+            __nanosleep(40);
         }
-    }
+        u32 slot[R]; ulonglong2 key[R]; u64 k1[R];
+        u32 todo = 0; // bit j: record j goes to the global word table
 #pragma unroll
-    for (int j = 0; j < R; j++) { // then use them
-        const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-        const u64 end = cta_base + rec[j].z; // buffer-relative offset of the delimiter
-        if (todo & (1u << j)) made += word_insert_at(T, k0, k1[j], delta, Lp->base + end, slot[j], key[j]);
-        else if (rec[j].w > 16) made += long_insert(Tp, Lp->buf, end - rec[j].w, rec[j].w, delta, Lp->base + end) << 8;
+        for (int j = 0; j < R; j++) {
+            if (!(live & (1u << j))) { rec[j] = make_uint4(0, 0, 0, 0); continue; }
+            const u32 len = rec[j].w;
+            if (len <= 8) { // still room in the CTA's table?
+                const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
+                const u32 sidx = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
+                const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[sidx]), 0ull, k0);
+                if (old == 0 || old == k0) {
+                    u32 *cell = reinterpret_cast<u32 *>(&tab[sidx]);
+                    atomicAdd(cell + 2, (u32)delta);
+                    atomicMin(cell + 3, rec[j].z);
+                } else { todo |= 1u << j; n_spill++; }
+            } else if (len <= 16) todo |= 1u << j;
+        }
+#pragma unroll
+        for (int j = 0; j < R; j++) { // issue every global read of the batch ...
+            const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
+            slot[j] = 0; key[j] = make_ulonglong2(0, 0); k1[j] = 0;
+            if (todo & (1u << j)) {
+                slot[j] = word_home(T, k0, rec[j].w);
+                key[j] = __ldcg(&T.w_keys[slot[j]]);
+                if (rec[j].w > 8) k1[j] = load8_unaligned(Lp->buf, cta_base + rec[j].z - rec[j].w + 8, rec[j].w - 8);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < R; j++) { // ... before the first one is used
+            const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
+            const u64 end = cta_base + rec[j].z; // buffer-relative offset of the delimiter
+            if (todo & (1u << j)) n_wnew += word_insert_at(T, k0, k1[j], delta, Lp->base + end, slot[j], key[j]);
+            else if (rec[j].w > 16) n_xnew += long_insert(Tp, Lp->buf, end - rec[j].w, rec[j].w, delta, Lp->base + end);
+        }
+        if (finished || vc->abort_flag) break;
     }
-    __syncwarp();
-    // move what is left to the front of the queue
-    for (u32 base = 0; base + take < count; base += 32) {
-        uint4 mv = make_uint4(0, 0, 0, 0);
-        const bool keep = base + lane + take < count;
-        if (keep) mv = q[base + lane + take];
-        __syncwarp();
-        if (keep) q[base + lane] = mv;
-        __syncwarp();
+    n_wnew = __reduce_add_sync(0xFFFFFFFFu, n_wnew);
+    n_xnew = __reduce_add_sync(0xFFFFFFFFu, n_xnew);
+    n_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
+    if (lane == 0) {
+        if (n_wnew) atomicAdd(&T.st->w_entries, (u64)n_wnew);
+        if (n_xnew) atomicAdd(&T.st->x_entries, (u64)n_xnew);
+        if (n_spill && !Lp->negate) atomicAdd(&T.st->n_spill, (u64)n_spill);
     }
-    return made;
 }
 
-__device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
 
 // One lane's two 16-byte pieces of tile `tile` into its buffer: asynchronous copies when the
 // bytes are all inside the input, a padded synchronous load at the very end of it.
@@ -501,9 +544,11 @@ extern __shared__ __align__(16) unsigned char wc_smem[];
 __global__ void __launch_bounds__(kThreads, 1)
 count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T) {
     uint4 *tab = reinterpret_cast<uint4 *>(wc_smem);
-    unsigned char *warp_all = wc_smem + kSmemTableBytes;
+    uint4 *def_ring = reinterpret_cast<uint4 *>(wc_smem + kSmemTableBytes);
+    unsigned char *warp_all = wc_smem + kSmemTableBytes + kDefRingBytes;
     __shared__ u32 s_first_ws;
     __shared__ u64 s_stop;
+    __shared__ DefCtl s_ctl;
     __shared__ uint2 s_keep[17]; // s_keep[n]: mask that keeps the first n bytes of an 8-byte key (n >= 8: all)
 
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -553,27 +598,31 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     const u32 delta32 = L.negate ? 0xFFFFFFFFu : 1u;
 
     for (u32 i = tid; i < kSmemEntries; i += kThreads) tab[i] = make_uint4(0, 0, 0, 0xFFFFFFFFu);
+    for (u32 i = tid; i < kDefRing; i += kThreads) def_ring[i] = make_uint4(0, 0, 0, 0);
+    if (tid == 0) { s_ctl.tail = 0; s_ctl.head = 0; s_ctl.done = 0; s_ctl.abort_flag = 0; }
     __syncthreads();
 
-    // per-warp shared memory: [two tile buffers] [delimiter list] [deferred words]
+    const u64 cta_base = (u64)blockIdx.x * kProducers * L.tiles_per_warp * kTile; // buffer-relative
+    if (warp >= (u32)kProducers) { // ---- consumer warps: everything that needs global memory
+        consume_deferred(def_ring, &s_ctl, &L, &T, cta_base, tab);
+    } else { // ---- producer warps: tokenize and count
+
+    // per-warp shared memory: [two tile buffers] [delimiter list]
     unsigned char *wbase = warp_all + warp * kWarpSmemBytes;
     unsigned short *dl = reinterpret_cast<unsigned short *>(wbase + kRingBytes);
-    uint4 *dq = reinterpret_cast<uint4 *>(wbase + kRingBytes + kDlBytes);
 
     const u32 tiles_total = (u32)((L.n + kTile - 1) / kTile);
-    const u32 gwarp = blockIdx.x * kWarps + warp;
+    const u32 gwarp = blockIdx.x * kProducers + warp;
     u32 t0 = gwarp * L.tiles_per_warp < tiles_total ? gwarp * L.tiles_per_warp : tiles_total;
     const u32 t1 = t0 + L.tiles_per_warp < tiles_total ? t0 + L.tiles_per_warp : tiles_total;
-    const u64 cta_base = (u64)blockIdx.x * kWarps * L.tiles_per_warp * kTile; // buffer-relative
     if (range_lo > 0 && t0 < t1) { // roll-back: start at the tile that holds range_lo
         const u64 tl = range_lo / kTile;
         if (tl >= t1) t0 = t1; else if (tl > t0) t0 = (u32)tl;
     }
     const u32 lt_mask = (1u << lane) - 1;
 
-    u32 n_wnew = 0, n_xnew = 0, n_spill = 0, n_long = 0; // per lane: new global slots, misses, 9+ byte words
+    u32 n_long = 0;                                  // per lane: words of 9+ bytes
     u32 acc_flush = 0, acc_empty = 0, acc_slow = 0;  // per lane; a warp's range is < 4 GiB
-    u32 q_count = 0;
     bool seen_nonempty = L.negate != 0;              // roll-back launches do not look for P0
     u32 p0_rel = 0, my_empties_before = 0;           // P0 relative to cta_base
 
@@ -770,18 +819,20 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const bool defer = word && !hit;
 #endif
                     const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
-                    if (bq) {
-                        if (defer) dq[q_count + __popc(bq & lt_mask)] = make_uint4(klo, khi, rel, (u32)len);
-                        n_long += defer && len > 8;
-                        q_count += __popc(bq);
-                        __syncwarp();
-                        if (q_count >= (u32)kDrainBatch) {
-#ifndef WC_EXP_NODRAIN
-                            const u32 made = drain_deferred(dq, q_count, kDrainBatch, &L, &T, cta_base, tab);
-                            n_wnew += made & 0xFFu; n_xnew += (made >> 8) & 0xFFu; n_spill += made >> 16;
-#endif
-                            q_count -= kDrainBatch;
+                    if (bq) { // hand the misses and the 9+ byte words to the consumer warps
+                        u32 at = 0;
+                        if (lane == 0) at = atomicAdd(&s_ctl.tail, (u32)__popc(bq));
+                        at = (__shfl_sync(0xFFFFFFFFu, at, 0) + __popc(bq & lt_mask)) & (kDefRing - 1);
+                        u32 spins = 0;
+                        while (__any_sync(0xFFFFFFFFu, defer && reinterpret_cast<volatile uint4 *>(def_ring)[at].w != 0)) {
+                            if (++spins > (1u << 24) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag)) {
+                                s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break;
+                            }
                         }
+#ifndef WC_EXP_NODRAIN
+                        if (defer) def_ring[at] = make_uint4(klo, khi, rel, (u32)len);
+#endif
+                        n_long += defer && len > 8;
                     }
                 }
                 if (total > 0) first_prev = (int)(dl[total - 1] & 0x3FFu);
@@ -790,24 +841,15 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             // the next tile sees this tile's last delimiter at a negative position
             carry_prev = first_prev - kTile < -(1 << 30) ? -(1 << 30) : first_prev - kTile;
         }
-        if (q_count > 0) { // at most kQueue - 1 records: one call takes them all (4 per lane, then the rest)
-            u32 made = drain_deferred(dq, q_count, q_count < (u32)kDrainBatch ? q_count : kDrainBatch, &L, &T, cta_base, tab);
-            if (q_count > (u32)kDrainBatch) made += drain_deferred(dq, q_count - kDrainBatch, q_count - kDrainBatch, &L, &T, cta_base, tab);
-            n_wnew += made & 0xFFu; n_xnew += (made >> 8) & 0xFFu; n_spill += made >> 16;
-        }
     }
-
     // ---- per-warp results
     const u64 w_flush = warp_sum64(acc_flush), w_empty = warp_sum64(acc_empty);
-    const u32 w_xnew = __reduce_add_sync(0xFFFFFFFFu, n_xnew);
-    const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, n_long), w_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
+    const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, n_long);
     if (lane == 0) {
         if (w_flush) atomicAdd(&st->n_flush, L.negate ? (u64)(-(long long)w_flush) : w_flush);
         if (w_empty) atomicAdd(&st->n_empty, L.negate ? (u64)(-(long long)w_empty) : w_empty);
-        if (w_xnew) atomicAdd(&st->x_entries, (u64)w_xnew);
         if (!L.negate) {
             if (w_long) atomicAdd(&st->n_long, (u64)w_long);
-            if (w_spill) atomicAdd(&st->n_spill, (u64)w_spill);
             if (acc_slow) atomicAdd(&st->n_slow_tiles, (u64)acc_slow);
             if (L.ws != nullptr && gwarp < L.n_ws) {
                 L.ws[gwarp].p0 = (seen_nonempty && t0 < t1) ? L.base + cta_base + p0_rel : kNone;
@@ -817,8 +859,13 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
         }
     }
 
+    __syncwarp();
+    if (lane == 0) atomicAdd(&s_ctl.done, 1u); // this producer will append nothing more
+    } // producer warps
+
     // ---- flush the CTA's table into the global one
     __syncthreads();
+    u32 n_wnew = 0;
     for (u32 i = tid; i < kSmemEntries; i += kThreads) {
         const uint4 ent = tab[i];
         if ((ent.x | ent.y) != 0 && ent.z != 0) {

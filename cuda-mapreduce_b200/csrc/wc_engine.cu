@@ -180,7 +180,7 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     CK(cudaMalloc((void **)&e->d_status, sizeof(wc::Status)));
     CK(cudaMallocHost((void **)&e->h_status, sizeof(wc::Status)));
     e->T.st = e->d_status;
-    e->n_ws = (u32)e->grid * wc::kWarps;
+    e->n_ws = (u32)e->grid * wc::kProducers;
     CK(cudaMalloc((void **)&e->d_ws, sizeof(wc::WarpSummary) * e->n_ws));
     int rc = alloc_tables(e, c.short_table_log2, c.long_table_log2, c.arena_bytes, &e->T, &e->table_block,
                           &e->table_block_bytes);
@@ -226,9 +226,9 @@ int wc_reset(wc_engine *e) {
 static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
     if (n == 0) return WC_OK;
     const u64 tiles = (n + wc::kTile - 1) / wc::kTile;
-    const u64 warps = (u64)e->grid * wc::kWarps;
+    const u64 warps = (u64)e->grid * wc::kProducers;
     const u64 tpw = (tiles + warps - 1) / warps;
-    if (tpw * wc::kWarps * wc::kTile >= 0xFFFFFFF0ull) { e->err = "piece too large for one launch"; return WC_ERR_TOO_LARGE; }
+    if (tpw * wc::kProducers * wc::kTile >= 0xFFFFFFF0ull) { e->err = "piece too large for one launch"; return WC_ERR_TOO_LARGE; }
     wc::Launch L;
     L.buf = dev; L.n = n; L.base = e->cfg.base_offset + e->consumed;
     L.tiles_per_warp = (u32)tpw; L.last_piece = last_piece; L.negate = 0;
@@ -746,7 +746,7 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
             }
             sd.scratch = (unsigned char *)addr; sd.num_sms = sms; sd.ready = true;
         }
-        const u32 n_ws = (u32)sd.num_sms * wc::kWarps;
+        const u32 n_ws = (u32)sd.num_sms * wc::kProducers;
         if (n_ws > kStaticMaxWarps) {
             rc = static_fail(WC_ERR_TOO_LARGE, "wc_count_device_static: this GPU has more SMs than the static scratch covers", cudaSuccess);
             break;
@@ -769,7 +769,7 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
         static_begin_kernel<<<1, 32, 0, stream>>>(st);
         if (n > 0) {
             const u64 tiles = (n + wc::kTile - 1) / wc::kTile;
-            const u64 warps = (u64)sd.num_sms * wc::kWarps;
+            const u64 warps = (u64)sd.num_sms * wc::kProducers;
             const u64 tpw = (tiles + warps - 1) / warps;
             wc::Launch L;
             L.buf = (const uint8_t *)dev_text; L.n = n; L.base = 0; L.tiles_per_warp = (u32)tpw;
