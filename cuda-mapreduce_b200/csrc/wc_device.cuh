@@ -19,10 +19,10 @@ typedef unsigned long long u64;
 typedef unsigned int u32;
 
 #ifndef WC_WARPS
-#define WC_WARPS 16
+#define WC_WARPS 24
 #endif
 #ifndef WC_CONSUMERS
-#define WC_CONSUMERS 2
+#define WC_CONSUMERS 8
 #endif
 #ifndef WC_DRAIN
 #define WC_DRAIN 64
@@ -825,9 +825,10 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                         at = (__shfl_sync(0xFFFFFFFFu, at, 0) + __popc(bq & lt_mask)) & (kDefRing - 1);
                         u32 spins = 0;
                         while (__any_sync(0xFFFFFFFFu, defer && reinterpret_cast<volatile uint4 *>(def_ring)[at].w != 0)) {
-                            if (++spins > (1u << 24) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag)) {
+                            if (++spins > (1u << 22) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag)) {
                                 s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break;
                             }
+                            __nanosleep(64); // the ring is full: leave the issue slots to the consumers
                         }
 #ifndef WC_EXP_NODRAIN
                         if (defer) def_ring[at] = make_uint4(klo, khi, rel, (u32)len);
