@@ -40,6 +40,7 @@ constexpr int kDlBytes = kDlCap * 2;
 constexpr int kDrainBatch = WC_DRAIN;      // deferred words a consumer warp takes at a time (WC_DRAIN / 32 per lane)
 constexpr u32 kDefRing = 1024;             // per CTA: ring of deferred-word records (16 bytes each)
 constexpr u64 kNone = ~0ull;
+constexpr u32 kMaxWordProbes = 128;        // longer probe chains in the global word table mean: grow it
 
 constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes;
 constexpr size_t kDefRingBytes = (size_t)kDefRing * 16;
@@ -66,6 +67,7 @@ struct Status {
     u64 arena_used;   // 8-byte units handed out (unit 0 is never used)
     u64 p0;           // offset that flushed the first non-empty word
     u64 lost_empty;   // empty words before p0 (main.cu:81,103: lost)
+    u64 ovf_count;    // records appended to the overflow log (may exceed its capacity: then err is set)
     u32 p0_found;
     u32 err;
 };
@@ -80,6 +82,10 @@ struct Tables {
     u32 x_log2;
     u64 *arena;       // unit[i] = length, unit[i+1..] = bytes, zero padded to 8
     u64 arena_units;
+    // Words the word table could not take (too full) are not lost: they go, as {key0, key1, count,
+    // first}, to this log, and the host replays it after re-hashing the table into a larger one.
+    u64 *ovf_log;     // 4 words per record
+    u64 ovf_cap;      // records
     Status *st;
 };
 
@@ -222,7 +228,14 @@ __device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u
         }
         if (k.x == k0 && k.y == k1) break;
         slot = (slot + 1) & mask;
-        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrWordFull); return 0; }
+        if (probes >= kMaxWordProbes || probes >= mask) { // the table is too full here: defer to the host
+            const u64 at = atomicAdd(&T.st->ovf_count, 1ull);
+            if (at < T.ovf_cap) {
+                T.ovf_log[4 * at] = k0; T.ovf_log[4 * at + 1] = k1;
+                T.ovf_log[4 * at + 2] = delta; T.ovf_log[4 * at + 3] = first_abs;
+            } else atomicOr(&T.st->err, kErrWordFull);
+            return 0;
+        }
         k = __ldcg(&T.w_keys[slot]);
     }
     atomicAdd(&T.w_counts[slot], delta); // both fire-and-forget (RED)

@@ -44,6 +44,8 @@ struct wc_engine {
     int ring = 0;
     std::vector<uint8_t> carry; // bytes after the last '\n' seen so far (an unfinished line)
 
+    u64 *d_ovf = nullptr;       // overflow log (wc::Tables::ovf_log)
+    u64 ovf_cap = 0;
     u64 *d_cursors = nullptr;   // shuffle: per-partition counts / cursors (2 * kMaxParts + 2 words)
     bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
     u64 job_bytes = 0;
@@ -51,6 +53,7 @@ struct wc_engine {
     u64 consumed = 0; // bytes handed to the device so far
     u64 fed = 0;      // bytes given to wc_feed / wc_count_device
     u64 launches = 0;
+    u64 pieces = 0;      // pieces launched since the last reset
     u64 grows = 0;
 
     // timing: per piece, events before the count kernel, after it, and after its roll-back companion
@@ -144,6 +147,7 @@ void wc_destroy(wc_engine *e) {
     if (e->d_status) cudaFree(e->d_status);
     if (e->d_ws) cudaFree(e->d_ws);
     if (e->d_cursors) cudaFree(e->d_cursors);
+    if (e->d_ovf) cudaFree(e->d_ovf);
     if (e->h_status) cudaFreeHost(e->h_status);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
@@ -182,6 +186,9 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     e->T.st = e->d_status;
     e->n_ws = (u32)e->grid * wc::kProducers;
     CK(cudaMalloc((void **)&e->d_ws, sizeof(wc::WarpSummary) * e->n_ws));
+    e->ovf_cap = 8ull << 20; // 8 Mi records (256 MiB): more words than a 64 MiB chunk can hold
+    CK(cudaMalloc((void **)&e->d_ovf, e->ovf_cap * 32));
+    e->T.ovf_log = e->d_ovf; e->T.ovf_cap = e->ovf_cap;
     int rc = alloc_tables(e, c.short_table_log2, c.long_table_log2, c.arena_bytes, &e->T, &e->table_block,
                           &e->table_block_bytes);
     if (rc != WC_OK) return rc;
@@ -214,13 +221,63 @@ int wc_reset(wc_engine *e) {
     if (rc != WC_OK) return rc;
     e->carry.clear();
     e->job_stats_set = false; e->job_bytes = 0;
-    e->consumed = 0; e->fed = 0; e->launches = 0; e->device_ms = 0; e->count_kernel_ms = 0;
+    e->consumed = 0; e->fed = 0; e->launches = 0; e->pieces = 0; e->device_ms = 0; e->count_kernel_ms = 0;
     for (auto &p : e->ev_used) { e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.mid); e->ev_pool.push_back(p.b); }
     e->ev_used.clear();
     return WC_OK;
 }
 
 } // extern "C"
+
+// Re-hashes the word table into one with 2^new_log2 slots (stream ordered).
+static int grow_word_table(wc_engine *e, u32 new_log2) {
+    if (new_log2 > 32) { e->err = "word table cannot grow beyond 2^32 slots"; return WC_ERR_TABLE_FULL; }
+    const wc::Tables old = e->T;
+    void *old_block = e->table_block;
+    wc::Tables nt; void *nb = nullptr; size_t nbytes = 0;
+    int rc = alloc_tables(e, new_log2, old.x_log2, 0, &nt, &nb, &nbytes);
+    if (rc != WC_OK) return rc;
+    CK(cudaMemsetAsync(nb, 0, nbytes, e->stream));
+    // the long table moves as it is (same capacity): a plain copy of its three arrays
+    const size_t l_n = (size_t)1 << old.x_log2;
+    CK(cudaMemcpyAsync(nt.x_refs, old.x_refs, 3 * l_n * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
+    wc::rehash_words_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(nt, old.w_keys, old.w_counts, old.w_finv,
+                                                                  1ull << old.w_log2);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(e->stream));
+    CK(cudaFree(old_block));
+    e->T = nt; e->table_block = nb; e->table_block_bytes = nbytes;
+    e->cfg.short_table_log2 = new_log2;
+    e->grows++;
+    return WC_OK;
+}
+
+// After a sync: if words overflowed the table (or it is more than half full), grow it and replay the
+// overflow log.  Leaves e->h_status up to date.  No word is ever dropped: wc_device.cuh logs what the
+// table could not take.
+static int settle_tables(wc_engine *e) {
+    for (int round = 0; round < 8; round++) {
+        CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        const wc::Status st = *e->h_status;
+        const u64 cap = 1ull << e->T.w_log2;
+        if ((st.err & wc::kErrWordFull) != 0) return WC_OK; // the log itself overflowed: reported by the caller
+        if (st.ovf_count == 0 && st.w_entries * 2 <= cap) return WC_OK;
+        u32 want = e->T.w_log2;
+        while ((1ull << want) < 4 * (st.w_entries + st.ovf_count) && want < 32) want++;
+        if (want == e->T.w_log2 && st.ovf_count == 0) return WC_OK;
+        if (want > e->T.w_log2) { int rc = grow_word_table(e, want); if (rc != WC_OK) return rc; }
+        if (st.ovf_count) {
+            e->h_status->ovf_count = 0;
+            CK(cudaMemcpyAsync(&e->d_status->ovf_count, &e->h_status->ovf_count, sizeof(u64), cudaMemcpyHostToDevice, e->stream));
+            // replaying appends to the same log only if the new table overflows again (then: next round);
+            // records are consumed front to back, new ones land behind the ones being read
+            wc::import_words_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, (const wc::WordRecord *)e->d_ovf, st.ovf_count);
+            CK(cudaGetLastError());
+        }
+    }
+    return WC_OK;
+}
 
 // Launches the forward count of one piece and its roll-back/summary companion on e->stream.
 static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
@@ -279,6 +336,15 @@ static int feed_piece(wc_engine *e, const uint8_t *src, size_t n, int last_piece
         if (rc != WC_OK) return rc;
         CK(cudaEventRecord(e->ev_counted[s], e->stream));
         e->ring ^= 1;
+        // Keep the word table ahead of the vocabulary: after each of the first pieces, and then every
+        // eighth, wait for the piece and grow the table / replay the overflow log if needed.  One chunk
+        // can never overflow the log (it holds more records than a chunk has words).
+        e->pieces++;
+        if (e->pieces <= 4 || (e->pieces & 7) == 0) {
+            CK(cudaStreamSynchronize(e->stream));
+            rc = settle_tables(e);
+            if (rc != WC_OK) return rc;
+        }
         return WC_OK;
     }
     // a single line longer than the chunk: give it a buffer of its own
@@ -397,8 +463,9 @@ int wc_finish(wc_engine *e, wc_result **out) {
     CK(cudaSetDevice(e->device));
     int rc = wc_end_input(e);
     if (rc != WC_OK) return rc;
-    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
     rc = wc_sync(e);
+    if (rc != WC_OK) return rc;
+    rc = settle_tables(e);
     if (rc != WC_OK) return rc;
     e->carry.clear();
     const wc::Status st = *e->h_status;
@@ -506,8 +573,9 @@ int wc_shard_stats_get(wc_engine *e, wc_shard_stats *out) {
     if (!e || !out) return WC_ERR_INVALID;
     CK(cudaSetDevice(e->device));
     { int rc0 = wc_end_input(e); if (rc0 != WC_OK) return rc0; } // a shard's counters describe all of its bytes
-    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
     int rc = wc_sync(e);
+    if (rc != WC_OK) return rc;
+    rc = settle_tables(e);
     if (rc != WC_OK) return rc;
     const wc::Status st = *e->h_status;
     if (st.err) { e->err = "device tables full"; return WC_ERR_TABLE_FULL; }

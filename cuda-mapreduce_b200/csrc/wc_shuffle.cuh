@@ -83,6 +83,17 @@ __global__ void import_long_kernel(Tables T, const LongRecord *meta, u64 n, cons
     if ((threadIdx.x & 31) == 0 && made) atomicAdd(&T.st->x_entries, (u64)made);
 }
 
+// Table growth: every entry of the old word table into the new one (T already points at the new arrays).
+__global__ void rehash_words_kernel(Tables T, const ulonglong2 *old_keys, const u64 *old_counts, const u64 *old_finv,
+                                    u64 n_old) {
+    for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n_old; i += (u64)gridDim.x * blockDim.x) {
+        const ulonglong2 k = old_keys[i];
+        if (k.x == 0) continue;
+        const u32 len = k.y ? 8 + key_len8(k.y) : key_len8(k.x);
+        word_insert(T, k.x, k.y, len, old_counts[i], ~old_finv[i]);
+    }
+}
+
 __global__ void count_long_kernel(Tables T, u64 *out) { // out[0] entries, out[1] blob bytes (padded to 8 each)
     const u64 n = 1ull << T.x_log2;
     for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {

@@ -358,3 +358,29 @@ def test_key_owner_exchange_two_engines_one_gpu(pkg):
         assert got.firsts == [f for _, _, f in exp.rows]
         assert (got.stats["n_flush"], got.stats["n_empty"], got.stats["n_lost_empty"], got.stats["stop"]) == \
                (exp.n_flush, exp.n_empty, exp.n_lost_empty, exp.stop)
+
+
+def test_word_table_grows_instead_of_overflowing(pkg):
+    """A word table far too small for the vocabulary: words it cannot take go to the overflow log, the
+    host re-hashes into a larger table and replays the log -- nothing is lost (wc_engine.cu
+    settle_tables)."""
+    rng = random.Random(21)
+    vocab = [bytes(rng.choice(b"abcdefghijklmnopqrstuvwxyz") for _ in range(rng.randint(2, 14))) for _ in range(60000)]
+    words = [rng.choice(vocab) for _ in range(400000)]
+    lines, cur = [], []
+    for w in words:
+        cur.append(w)
+        if len(cur) == 12:
+            lines.append(b" ".join(cur)); cur = []
+    data = b"\n".join(lines) + b"\n"
+    with pkg.Engine(chunk_bytes=1 << 20, short_table_log2=10, long_table_log2=10, arena_bytes=1 << 20) as e:
+        got = check_against_oracle(e, data, what="grow")
+        assert got.stats["table_grows"] >= 1 and got.stats["n_distinct"] > 40000
+        # device-resident input in one piece: the same machinery at wc_finish
+        import torch
+        dev = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+    with pkg.Engine(short_table_log2=12, long_table_log2=10, arena_bytes=1 << 20) as e:
+        e.count_device(dev.data_ptr(), dev.numel(), last_piece=True)
+        got = e.finish()
+        exp = O.fast(data)
+        assert got.pairs() == exp.pairs() and got.total == exp.total and got.stats["table_grows"] >= 1
