@@ -52,7 +52,8 @@ static_assert(kSmemTotal <= 232448 - 64, "more shared memory than an sm_100 CTA 
 static_assert(kConsumers >= 1 && kProducers >= 1 && kDrainBatch % 32 == 0 && kDrainBatch <= 128, "bad build knobs");
 static_assert((kDefRing & (kDefRing - 1)) == 0 && kDefRing >= 4 * kDrainBatch, "ring size");
 
-enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u, kErrRingTimeout = 16u };
+enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u, kErrRingTimeout = 16u,
+             kErrEmitFull = 32u };
 
 // Device-resident job state (one per engine).
 struct Status {
@@ -95,6 +96,18 @@ struct WarpSummary { // per warp, in input order: what finding P0 needs
     u64 empties_total;
 };
 
+// Sort path (WC_PATH_SORT): instead of counting in hash tables, every word of 1..16 bytes is written
+// out as a record -- 64-bit hash (the sort key), the word itself (16 bytes, zero padded) and the offset
+// that flushed it -- to be radix-sorted and run-length reduced at the end of the job.
+struct EmitBuf {
+    u64 *cursor;       // records written so far (device counter); nullptr: hash path
+    u64 *hash;         // [cap] sort keys
+    u32 *idx;          // [cap] record index (the sort's payload)
+    ulonglong2 *key;   // [cap] the word, zero padded to 16 bytes
+    u64 *end;          // [cap] absolute offset of the delimiter that flushed it
+    u64 cap;
+};
+
 struct Launch {
     const uint8_t *buf; // 16-byte aligned, starts at a line start
     u64 n;
@@ -104,6 +117,7 @@ struct Launch {
     int negate;         // roll-back launch: subtract everything at or after Status::stop
     WarpSummary *ws;
     u32 n_ws;
+    EmitBuf em;
 };
 
 // ---------------------------------------------------------------- helpers
@@ -812,6 +826,44 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const uint2 keep = s_keep[rlen];
                     const u32 sh = (idx & 3) * 8;
                     const u32 klo = __funnelshift_r(w0, w1, sh) & keep.x, khi = __funnelshift_r(w1, w2, sh) & keep.y;
+
+                    if (L.em.cursor != nullptr) { // ---- sort path: write the word out instead of counting it
+                        const bool emit = word && len <= 16 && !L.negate; // (what lies after STOP is dropped at the end)
+                        const u32 be = __ballot_sync(0xFFFFFFFFu, emit);
+                        if (be) {
+                            u64 at = 0;
+                            if (lane == 0) at = atomicAdd(L.em.cursor, (u64)__popc(be));
+                            at = __shfl_sync(0xFFFFFFFFu, at, 0) + __popc(be & lt_mask);
+                            if (emit && at < L.em.cap) {
+                                u32 k1lo = 0, k1hi = 0;
+                                if (len > 8) { // bytes 8..15
+                                    const uint2 keep1 = s_keep[len - 8];
+                                    k1lo = __funnelshift_r(w2, r[3], sh) & keep1.x;
+                                    k1hi = __funnelshift_r(r[3], r[4], sh) & keep1.y;
+                                }
+                                const u64 k0 = (u64)klo | ((u64)khi << 32), k1 = (u64)k1lo | ((u64)k1hi << 32);
+                                L.em.hash[at] = mix64(k0 ^ mix64(k1 + 0x9E3779B97F4A7C15ull));
+                                L.em.idx[at] = (u32)at;
+                                L.em.key[at] = make_ulonglong2(k0, k1);
+                                L.em.end[at] = L.base + T0 + (u64)e;
+                            } else if (emit) atomicOr(&st->err, kErrEmitFull);
+                        }
+                        const bool dlong = word && len > 16; // the few longer words still go to the long table
+                        const u32 bl = __ballot_sync(0xFFFFFFFFu, dlong);
+                        if (bl) {
+                            u32 pos = 0;
+                            if (lane == 0) pos = atomicAdd(&s_ctl.tail, (u32)__popc(bl));
+                            pos = (__shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bl & lt_mask)) & (kDefRing - 1);
+                            u32 spins = 0;
+                            while (__any_sync(0xFFFFFFFFu, dlong && reinterpret_cast<volatile uint4 *>(def_ring)[pos].w != 0)) {
+                                if (++spins > (1u << 22)) { s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break; }
+                                __nanosleep(64);
+                            }
+                            if (dlong) def_ring[pos] = make_uint4(klo, khi, relT + (u32)e, (u32)len);
+                            n_long += dlong;
+                        }
+                        continue;
+                    }
 
                     // single-probe shared-memory table
                     const u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);

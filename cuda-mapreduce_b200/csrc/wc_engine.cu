@@ -14,6 +14,9 @@
 #include "../../include/wc.h"
 #include "wc_device.cuh"
 #include "wc_shuffle.cuh"
+#include "wc_sort.cuh"
+#include <cub/cub.cuh>
+#include <unordered_map>
 #include "wc_finalize.h"
 
 using wc::u32;
@@ -44,6 +47,10 @@ struct wc_engine {
     int ring = 0;
     std::vector<uint8_t> carry; // bytes after the last '\n' seen so far (an unfinished line)
 
+    // sort path (WC_PATH_SORT): one record per word of 1..16 bytes, sorted and reduced in wc_finish
+    bool sort_mode = false;
+    wc::EmitBuf em{};           // device buffers; em.cursor is always allocated in sort mode
+    u64 em_bound = 0;           // upper bound of records written so far (pieces launched)
     u64 *d_ovf = nullptr;       // overflow log (wc::Tables::ovf_log)
     u64 ovf_cap = 0;
     u64 *d_cursors = nullptr;   // shuffle: per-partition counts / cursors (2 * kMaxParts + 2 words)
@@ -106,6 +113,8 @@ static int reset_device_state(wc_engine *e) {
     s.stop = wc::kNone; s.p0 = wc::kNone; s.arena_used = 1;
     *e->h_status = s;
     CK(cudaMemcpyAsync(e->d_status, e->h_status, sizeof(s), cudaMemcpyHostToDevice, e->stream));
+    if (e->em.cursor) CK(cudaMemsetAsync(e->em.cursor, 0, sizeof(u64), e->stream));
+    e->em_bound = 0;
     return WC_OK;
 }
 
@@ -147,6 +156,11 @@ void wc_destroy(wc_engine *e) {
     if (e->d_status) cudaFree(e->d_status);
     if (e->d_ws) cudaFree(e->d_ws);
     if (e->d_cursors) cudaFree(e->d_cursors);
+    if (e->em.cursor) cudaFree(e->em.cursor);
+    if (e->em.hash) cudaFree(e->em.hash);
+    if (e->em.idx) cudaFree(e->em.idx);
+    if (e->em.key) cudaFree(e->em.key);
+    if (e->em.end) cudaFree(e->em.end);
     if (e->d_ovf) cudaFree(e->d_ovf);
     if (e->h_status) cudaFreeHost(e->h_status);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -192,6 +206,8 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     int rc = alloc_tables(e, c.short_table_log2, c.long_table_log2, c.arena_bytes, &e->T, &e->table_block,
                           &e->table_block_bytes);
     if (rc != WC_OK) return rc;
+    e->sort_mode = c.path == WC_PATH_SORT;
+    if (e->sort_mode) CK(cudaMalloc((void **)&e->em.cursor, sizeof(u64)));
     rc = reset_device_state(e);
     if (rc != WC_OK) return rc;
     CK(cudaStreamSynchronize(e->stream));
@@ -279,6 +295,112 @@ static int settle_tables(wc_engine *e) {
     return WC_OK;
 }
 
+// Sort path: room for the records of a piece of n more bytes (at most one word per two bytes).  The
+// number written so far is read back, so the bound stays tight from piece to piece.
+static int ensure_emit_capacity(wc_engine *e, size_t n) {
+    u64 have = 0;
+    if (e->em_bound > 0) {
+        CK(cudaStreamSynchronize(e->stream));
+        CK(cudaMemcpy(&have, e->em.cursor, sizeof(u64), cudaMemcpyDeviceToHost));
+    }
+    const u64 need = have + n / 2 + 64;
+    if (need >= 0xFFFFFFF0ull) { e->err = "sort path: more than 2^32 words in one job"; return WC_ERR_TOO_LARGE; }
+    if (need > e->em.cap) {
+        u64 cap = e->em.cap ? e->em.cap : 1;
+        while (cap < need) cap *= 2;
+        if (cap > 0xFFFFFFF0ull) cap = 0xFFFFFFF0ull;
+        wc::EmitBuf nb = e->em;
+        CK(cudaMalloc((void **)&nb.hash, cap * sizeof(u64)));
+        CK(cudaMalloc((void **)&nb.idx, cap * sizeof(u32)));
+        CK(cudaMalloc((void **)&nb.key, cap * sizeof(ulonglong2)));
+        CK(cudaMalloc((void **)&nb.end, cap * sizeof(u64)));
+        if (have) {
+            CK(cudaMemcpy(nb.hash, e->em.hash, have * sizeof(u64), cudaMemcpyDeviceToDevice));
+            CK(cudaMemcpy(nb.idx, e->em.idx, have * sizeof(u32), cudaMemcpyDeviceToDevice));
+            CK(cudaMemcpy(nb.key, e->em.key, have * sizeof(ulonglong2), cudaMemcpyDeviceToDevice));
+            CK(cudaMemcpy(nb.end, e->em.end, have * sizeof(u64), cudaMemcpyDeviceToDevice));
+        }
+        if (e->em.hash) { cudaFree(e->em.hash); cudaFree(e->em.idx); cudaFree(e->em.key); cudaFree(e->em.end); }
+        nb.cap = cap;
+        e->em = nb;
+    }
+    e->em_bound = need;
+    return WC_OK;
+}
+
+// Sort path, end of job: sort the records by hash, mark and number the runs of equal words, reduce
+// every run to (word, count, first offset) and append them to `entries` / `blob`.
+static int finish_sorted(wc_engine *e, u64 stop_abs, std::string &blob, std::vector<wc::HostEntry> &entries, u64 *n_words_out) {
+    u64 n = 0;
+    CK(cudaMemcpy(&n, e->em.cursor, sizeof(u64), cudaMemcpyDeviceToHost));
+    if (n > e->em.cap) n = e->em.cap;
+    *n_words_out = n;
+    if (n == 0) return WC_OK;
+    u64 *hash_alt = nullptr; u32 *idx_alt = nullptr, *flags = nullptr; void *temp = nullptr; u64 *d_coll = nullptr;
+    CK(cudaMalloc((void **)&hash_alt, n * sizeof(u64)));
+    CK(cudaMalloc((void **)&idx_alt, n * sizeof(u32)));
+    CK(cudaMalloc((void **)&flags, n * sizeof(u32)));
+    CK(cudaMalloc((void **)&d_coll, sizeof(u64)));
+    CK(cudaMemsetAsync(d_coll, 0, sizeof(u64), e->stream));
+    cub::DoubleBuffer<u64> dk(e->em.hash, hash_alt);
+    cub::DoubleBuffer<u32> dv(e->em.idx, idx_alt);
+    size_t tb_sort = 0, tb_scan = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tb_sort, dk, dv, n, 0, 64, e->stream));
+    CK(cub::DeviceScan::InclusiveSum(nullptr, tb_scan, flags, flags, n, e->stream));
+    const size_t tb = tb_sort > tb_scan ? tb_sort : tb_scan;
+    CK(cudaMalloc(&temp, tb ? tb : 16));
+    size_t tbx = tb;
+    CK(cub::DeviceRadixSort::SortPairs(temp, tbx, dk, dv, n, 0, 64, e->stream));
+    wc::sort_mark_heads_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(dk.Current(), dv.Current(), e->em.key, n, flags, d_coll);
+    tbx = tb;
+    CK(cub::DeviceScan::InclusiveSum(temp, tbx, flags, flags, n, e->stream)); // flags -> 1-based run numbers
+    u32 n_runs = 0; u64 coll = 0;
+    CK(cudaMemcpyAsync(&n_runs, flags + (n - 1), sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(&coll, d_coll, sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    ulonglong2 *o_key = nullptr; u64 *o_count = nullptr, *o_first = nullptr;
+    CK(cudaMalloc((void **)&o_key, (size_t)n_runs * sizeof(ulonglong2)));
+    CK(cudaMalloc((void **)&o_count, (size_t)n_runs * sizeof(u64)));
+    CK(cudaMalloc((void **)&o_first, (size_t)n_runs * sizeof(u64)));
+    CK(cudaMemsetAsync(o_count, 0, (size_t)n_runs * sizeof(u64), e->stream));
+    CK(cudaMemsetAsync(o_first, 0xFF, (size_t)n_runs * sizeof(u64), e->stream));
+    wc::sort_reduce_runs_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(dv.Current(), e->em.key, e->em.end, flags, n, stop_abs,
+                                                                      o_key, o_count, o_first);
+    CK(cudaGetLastError());
+    std::vector<u64> hk((size_t)n_runs * 2), hc(n_runs), hf(n_runs);
+    CK(cudaMemcpyAsync(hk.data(), o_key, hk.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(hc.data(), o_count, hc.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(hf.data(), o_first, hf.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->launches += 2;
+    cudaFree(hash_alt); cudaFree(idx_alt); cudaFree(flags); cudaFree(temp); cudaFree(d_coll);
+    cudaFree(o_key); cudaFree(o_count); cudaFree(o_first);
+
+    struct KeyHash { size_t operator()(const std::pair<u64, u64> &k) const { return (size_t)(k.first * 0x9E3779B97F4A7C15ull ^ k.second); } };
+    std::unordered_map<std::pair<u64, u64>, size_t, KeyHash> seen; // only if two words shared a hash
+    entries.reserve(entries.size() + n_runs);
+    for (u32 r = 0; r < n_runs; r++) {
+        const u64 k[2] = {hk[2 * (size_t)r], hk[2 * (size_t)r + 1]};
+        if (hc[r] == 0) continue;
+        if (coll) {
+            auto it = seen.find({k[0], k[1]});
+            if (it != seen.end()) {
+                wc::HostEntry &he = entries[it->second];
+                he.count += (int64_t)hc[r];
+                if (hf[r] < he.first) he.first = hf[r];
+                continue;
+            }
+            seen.emplace(std::make_pair(k[0], k[1]), entries.size());
+        }
+        const unsigned char *kb = (const unsigned char *)k;
+        u32 len = 16;
+        while (len > 1 && kb[len - 1] == 0) len--;
+        entries.push_back(wc::HostEntry{blob.size(), len, (int64_t)hc[r], hf[r]});
+        blob.append((const char *)kb, len);
+    }
+    return WC_OK;
+}
+
 // Launches the forward count of one piece and its roll-back/summary companion on e->stream.
 static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
     if (n == 0) return WC_OK;
@@ -290,6 +412,12 @@ static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_pie
     L.buf = dev; L.n = n; L.base = e->cfg.base_offset + e->consumed;
     L.tiles_per_warp = (u32)tpw; L.last_piece = last_piece; L.negate = 0;
     L.ws = e->d_ws; L.n_ws = e->n_ws;
+    memset(&L.em, 0, sizeof(L.em));
+    if (e->sort_mode) {
+        int rc = ensure_emit_capacity(e, n);
+        if (rc != WC_OK) return rc;
+        L.em = e->em;
+    }
 
     cudaEvent_t a, mid, b;
     for (cudaEvent_t *ev : {&a, &mid, &b}) {
@@ -499,6 +627,11 @@ int wc_finish(wc_engine *e, wc_result **out) {
         while (len > 1 && kb[len - 1] == 0) len--;
         entries.push_back(wc::HostEntry{blob.size(), len, (int64_t)w_counts[i], ~w_finv[i]});
         blob.append((const char *)kb, len);
+    }
+    if (e->sort_mode) {
+        u64 n_sorted = 0;
+        rc = finish_sorted(e, st.stop, blob, entries, &n_sorted);
+        if (rc != WC_OK) return rc;
     }
     for (size_t i = 0; i < l_n; i++) {
         const u64 r = x_refs[i];

@@ -8,6 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 MODE_REF = 0
 MODE_EXACT = 1
+PATH_AUTO, PATH_HASH, PATH_SORT = 0, 1, 2
 
 
 def lib_path():
@@ -169,11 +170,11 @@ class Engine:
     """with Engine(mode=...) as e: e.feed(bytes); res = e.finish()"""
 
     def __init__(self, mode=MODE_REF, device=0, chunk_bytes=0, short_table_log2=0, long_table_log2=0,
-                 arena_bytes=0, base_offset=0):
+                 arena_bytes=0, base_offset=0, path=0):
         L = lib()
         cfg = Config()
         L.wc_config_default(C.byref(cfg))
-        cfg.mode, cfg.device, cfg.base_offset = mode, device, base_offset
+        cfg.mode, cfg.device, cfg.base_offset, cfg.path = mode, device, base_offset, path
         if chunk_bytes:
             cfg.chunk_bytes = chunk_bytes
         if short_table_log2:

@@ -384,3 +384,27 @@ def test_word_table_grows_instead_of_overflowing(pkg):
         got = e.finish()
         exp = O.fast(data)
         assert got.pairs() == exp.pairs() and got.total == exp.total and got.stats["table_grows"] >= 1
+
+
+def test_sort_path_matches_oracle(pkg, golden):
+    """WC_PATH_SORT: records -> cub radix sort by hash -> runs of equal words -> (count, first).  Same
+    rows as the hash path and the oracle, on the golden vectors, fuzz, STOP cases and corpus samples."""
+    from tools.corpus import Corpus
+    rng = random.Random(77)
+    with pkg.Engine(path=pkg.PATH_SORT, chunk_bytes=1 << 20, **SMALL) as e:
+        for name, data, _ in golden:
+            if data is not None:
+                check_against_oracle(e, data, what=("sort", name))
+        for i in range(60):
+            data = random_text(rng, rng.randint(0, 400), weird=rng.choice([0.0, 0.05, 0.3]))
+            check_against_oracle(e, data, what=("sort fuzz", i))
+        base = random_text(rng, 30000, weird=0.0).replace(b"\n\n", b"\n")
+        check_against_oracle(e, base[:40000] + b"\n\n" + base[40000:], what="sort stop")
+    for cfg, nbytes in ((2, 24 << 20), (5, 9_000_000)):
+        data = Corpus(cfg, total_bytes=nbytes).bytes()
+        exp = O.fast_mt(data)
+        with pkg.Engine(path=pkg.PATH_SORT, chunk_bytes=4 << 20, short_table_log2=12, long_table_log2=14,
+                        arena_bytes=64 << 20) as e:
+            e.feed(data)
+            got = e.finish()
+        assert got.pairs() == exp.pairs() and got.total == exp.total and got.stats["n_flush"] == exp.n_flush
