@@ -106,6 +106,10 @@ def workload_params(name, n_gpus):
         total = CONFIGS[3]["bytes"]
         return dict(config=3, total=total, per_gpu=total // n_gpus, s_log2=22, l_log2=14,
                     label="config3: Zipf(1.1) text, 1M-word vocabulary, 1.6e10 B over all GPUs")
+    if name == "config5":
+        per_gpu = CONFIGS[5]["bytes"]
+        return dict(config=5, total=per_gpu * n_gpus, per_gpu=per_gpu, s_log2=30, l_log2=16,
+                    label="config5: adversarial text, ~90 % unique 8-16 byte tokens, 4e9 B per GPU")
     raise SystemExit("unknown workload " + name)
 
 
@@ -150,6 +154,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="config2")
+    ap.add_argument("--bytes", type=int, default=0, help="override the per-GPU input size (profiling / sweeps)")
+    ap.add_argument("--path", default="auto", choices=["auto", "hash", "sort"], help="aggregation path (wc_config.path)")
+    ap.add_argument("--table-log2", type=int, default=0, help="override the word table size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
     args = ap.parse_args()
@@ -174,6 +181,14 @@ def main():
     from cuda_mapreduce_b200 import multi
     shard_range = multi.shard_range
     wp = workload_params(args.workload, world)
+    if args.bytes:
+        wp["per_gpu"] = args.bytes
+        wp["total"] = args.bytes * world
+        wp["label"] += " (size overridden: %d B per GPU)" % args.bytes
+    if args.table_log2:
+        wp["s_log2"] = args.table_log2
+    if args.path == "sort":
+        wp["s_log2"] = 12
 
     # ---- this rank's shard of the synthetic corpus, generated into pinned host memory
     corpus = Corpus(wp["config"], total_bytes=wp["total"])
@@ -183,7 +198,8 @@ def main():
     corpus.fill(host.numpy(), lo, nbytes)
     dev = host.cuda(non_blocking=False)
 
-    eng = pkg.Engine(device=local_rank, short_table_log2=wp["s_log2"], long_table_log2=wp["l_log2"], base_offset=lo)
+    eng = pkg.Engine(device=local_rank, short_table_log2=wp["s_log2"], long_table_log2=wp["l_log2"], base_offset=lo,
+                     path={"auto": 0, "hash": 1, "sort": 2}[args.path])
     ext = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local_rank))
 
     def barrier():
@@ -197,6 +213,8 @@ def main():
     def step_device():
         eng.reset()
         eng.count_device(dev.data_ptr(), nbytes, last_piece=(rank == world - 1))
+        if args.path == "sort":
+            eng.aggregate()  # radix sort + run reduce: the sort path's counterpart of the hash tables
         if world > 1:  # key-owner exchange: NCCL all-to-all, owner reduce, gather on rank 0
             with torch.cuda.stream(ext):
                 multi.exchange_and_gather(eng, devt)

@@ -51,6 +51,8 @@ struct wc_engine {
     bool sort_mode = false;
     wc::EmitBuf em{};           // device buffers; em.cursor is always allocated in sort mode
     u64 em_bound = 0;           // upper bound of records written so far (pieces launched)
+    ulonglong2 *so_key = nullptr; u64 *so_count = nullptr, *so_first = nullptr; // wc_aggregate()'s output
+    u32 so_runs = 0; u64 so_coll = 0, so_words = 0; bool so_valid = false;
     u64 *d_ovf = nullptr;       // overflow log (wc::Tables::ovf_log)
     u64 ovf_cap = 0;
     u64 *d_cursors = nullptr;   // shuffle: per-partition counts / cursors (2 * kMaxParts + 2 words)
@@ -115,6 +117,7 @@ static int reset_device_state(wc_engine *e) {
     CK(cudaMemcpyAsync(e->d_status, e->h_status, sizeof(s), cudaMemcpyHostToDevice, e->stream));
     if (e->em.cursor) CK(cudaMemsetAsync(e->em.cursor, 0, sizeof(u64), e->stream));
     e->em_bound = 0;
+    e->so_valid = false;
     return WC_OK;
 }
 
@@ -156,6 +159,7 @@ void wc_destroy(wc_engine *e) {
     if (e->d_status) cudaFree(e->d_status);
     if (e->d_ws) cudaFree(e->d_ws);
     if (e->d_cursors) cudaFree(e->d_cursors);
+    if (e->so_key) { cudaFree(e->so_key); cudaFree(e->so_count); cudaFree(e->so_first); }
     if (e->em.cursor) cudaFree(e->em.cursor);
     if (e->em.hash) cudaFree(e->em.hash);
     if (e->em.idx) cudaFree(e->em.idx);
@@ -328,13 +332,18 @@ static int ensure_emit_capacity(wc_engine *e, size_t n) {
     return WC_OK;
 }
 
-// Sort path, end of job: sort the records by hash, mark and number the runs of equal words, reduce
-// every run to (word, count, first offset) and append them to `entries` / `blob`.
-static int finish_sorted(wc_engine *e, u64 stop_abs, std::string &blob, std::vector<wc::HostEntry> &entries, u64 *n_words_out) {
+// Sort path, device half: sort the records by hash, mark and number the runs of equal words, reduce
+// every run to (word, count, first offset).  The result stays in device memory (e->so_*).
+static int sort_aggregate(wc_engine *e, u64 stop_abs) {
+    if (e->so_valid) return WC_OK;
+    if (e->so_key) { cudaFree(e->so_key); cudaFree(e->so_count); cudaFree(e->so_first); e->so_key = nullptr; }
+    e->so_runs = 0; e->so_coll = 0;
     u64 n = 0;
+    CK(cudaStreamSynchronize(e->stream));
     CK(cudaMemcpy(&n, e->em.cursor, sizeof(u64), cudaMemcpyDeviceToHost));
     if (n > e->em.cap) n = e->em.cap;
-    *n_words_out = n;
+    e->so_words = n;
+    e->so_valid = true;
     if (n == 0) return WC_OK;
     u64 *hash_alt = nullptr; u32 *idx_alt = nullptr, *flags = nullptr; void *temp = nullptr; u64 *d_coll = nullptr;
     CK(cudaMalloc((void **)&hash_alt, n * sizeof(u64)));
@@ -358,23 +367,37 @@ static int finish_sorted(wc_engine *e, u64 stop_abs, std::string &blob, std::vec
     CK(cudaMemcpyAsync(&n_runs, flags + (n - 1), sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(&coll, d_coll, sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
-    ulonglong2 *o_key = nullptr; u64 *o_count = nullptr, *o_first = nullptr;
-    CK(cudaMalloc((void **)&o_key, (size_t)n_runs * sizeof(ulonglong2)));
-    CK(cudaMalloc((void **)&o_count, (size_t)n_runs * sizeof(u64)));
-    CK(cudaMalloc((void **)&o_first, (size_t)n_runs * sizeof(u64)));
-    CK(cudaMemsetAsync(o_count, 0, (size_t)n_runs * sizeof(u64), e->stream));
-    CK(cudaMemsetAsync(o_first, 0xFF, (size_t)n_runs * sizeof(u64), e->stream));
+    CK(cudaMalloc((void **)&e->so_key, (size_t)n_runs * sizeof(ulonglong2)));
+    CK(cudaMalloc((void **)&e->so_count, (size_t)n_runs * sizeof(u64)));
+    CK(cudaMalloc((void **)&e->so_first, (size_t)n_runs * sizeof(u64)));
+    CK(cudaMemsetAsync(e->so_count, 0, (size_t)n_runs * sizeof(u64), e->stream));
+    CK(cudaMemsetAsync(e->so_first, 0xFF, (size_t)n_runs * sizeof(u64), e->stream));
     wc::sort_reduce_runs_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(dv.Current(), e->em.key, e->em.end, flags, n, stop_abs,
-                                                                      o_key, o_count, o_first);
+                                                                      e->so_key, e->so_count, e->so_first);
     CK(cudaGetLastError());
-    std::vector<u64> hk((size_t)n_runs * 2), hc(n_runs), hf(n_runs);
-    CK(cudaMemcpyAsync(hk.data(), o_key, hk.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
-    CK(cudaMemcpyAsync(hc.data(), o_count, hc.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
-    CK(cudaMemcpyAsync(hf.data(), o_first, hf.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    // the sort may have left the records in the alternate buffers: make them the current ones
+    if (dk.Current() != e->em.hash) { std::swap(e->em.hash, hash_alt); }
+    if (dv.Current() != e->em.idx) { std::swap(e->em.idx, idx_alt); }
     e->launches += 2;
+    e->so_runs = n_runs; e->so_coll = coll;
     cudaFree(hash_alt); cudaFree(idx_alt); cudaFree(flags); cudaFree(temp); cudaFree(d_coll);
-    cudaFree(o_key); cudaFree(o_count); cudaFree(o_first);
+    return WC_OK;
+}
+
+// Sort path, host half: bring the runs over and append them to `entries` / `blob`.
+static int finish_sorted(wc_engine *e, u64 stop_abs, std::string &blob, std::vector<wc::HostEntry> &entries, u64 *n_words_out) {
+    int rc = sort_aggregate(e, stop_abs);
+    if (rc != WC_OK) return rc;
+    *n_words_out = e->so_words;
+    const u32 n_runs = e->so_runs;
+    const u64 coll = e->so_coll;
+    if (n_runs == 0) return WC_OK;
+    std::vector<u64> hk((size_t)n_runs * 2), hc(n_runs), hf(n_runs);
+    CK(cudaMemcpyAsync(hk.data(), e->so_key, hk.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(hc.data(), e->so_count, hc.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(hf.data(), e->so_first, hf.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
 
     struct KeyHash { size_t operator()(const std::pair<u64, u64> &k) const { return (size_t)(k.first * 0x9E3779B97F4A7C15ull ^ k.second); } };
     std::unordered_map<std::pair<u64, u64>, size_t, KeyHash> seen; // only if two words shared a hash
@@ -417,6 +440,7 @@ static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_pie
         int rc = ensure_emit_capacity(e, n);
         if (rc != WC_OK) return rc;
         L.em = e->em;
+        e->so_valid = false;
     }
 
     cudaEvent_t a, mid, b;
@@ -553,6 +577,17 @@ int wc_sync(wc_engine *e) {
     }
     e->ev_used.clear();
     return WC_OK;
+}
+
+int wc_aggregate(wc_engine *e) {
+    if (!e) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    if (!e->sort_mode) return WC_OK; // the hash tables are the aggregate already
+    int rc = wc_end_input(e);
+    if (rc != WC_OK) return rc;
+    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return sort_aggregate(e, e->h_status->stop);
 }
 
 int wc_device_ms(wc_engine *e, double *ms, double *count_kernel_ms, uint64_t *kernel_launches) {

@@ -82,6 +82,7 @@ def lib():
     L.wc_count_device.argtypes = [vp, vp, sz, C.c_int]
     L.wc_sync.argtypes = [vp]
     L.wc_end_input.argtypes = [vp]
+    L.wc_aggregate.argtypes = [vp]
     L.wc_finish.argtypes = [vp, C.POINTER(vp)]
     L.wc_result_rows.argtypes = [vp]
     L.wc_result_rows.restype = sz
@@ -209,6 +210,9 @@ class Engine:
 
     def count_device(self, dev_ptr, n, last_piece=True):
         self._ck(lib().wc_count_device(self.h, C.c_void_p(dev_ptr), n, 1 if last_piece else 0))
+
+    def aggregate(self):
+        self._ck(lib().wc_aggregate(self.h))
 
     def sync(self):
         self._ck(lib().wc_sync(self.h))

@@ -112,6 +112,11 @@ WC_API int wc_count_device(wc_engine *e, const void *dev_bytes, size_t n, int la
  * like in main.cu:198-203).  wc_finish and wc_shard_stats_get call it themselves. */
 WC_API int wc_end_input(wc_engine *e);
 
+/* Completes the device-side aggregation of what has been fed so far.  On the hash path the tables
+ * are always aggregated and this does nothing; on the sort path (WC_PATH_SORT) it runs the radix sort
+ * and the run reduce and leaves (word, count, first) triples in device memory.  wc_finish calls it. */
+WC_API int wc_aggregate(wc_engine *e);
+
 /* Wait for everything queued so far. */
 WC_API int wc_sync(wc_engine *e);
 
