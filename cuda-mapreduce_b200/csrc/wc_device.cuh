@@ -267,6 +267,14 @@ __device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u32 
 __device__ __forceinline__ u64 long_hash(const uint8_t *buf, u64 start, u64 len) {
     u64 h = 0x9E3779B97F4A7C15ull ^ (len * 0xFF51AFD7ED558CCDull);
     u64 i = 0;
+    for (; i + 32 <= len; i += 32) { // four loads in flight per step: very long words are latency bound
+        const u64 a = load8_unaligned(buf, start + i), b = load8_unaligned(buf, start + i + 8);
+        const u64 c = load8_unaligned(buf, start + i + 16), d = load8_unaligned(buf, start + i + 24);
+        h = (h ^ a) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
+        h = (h ^ b) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
+        h = (h ^ c) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
+        h = (h ^ d) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
+    }
     for (; i + 8 <= len; i += 8) {
         h = (h ^ load8_unaligned(buf, start + i)) * 0x9FB21C651E98DF25ull;
         h ^= h >> 32;
@@ -453,13 +461,35 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
 //                 table fills up), else count it in the global word table;
 //   9..16 bytes : fetch bytes 8..15 from the text, count in the global word table;
 //   17+ bytes   : the arena-backed long table.
-// Ring protocol: producers reserve positions with one atomicAdd on `tail` per warp and round, wait
-// until the position's previous occupant has been taken (record.w == 0) and store the record with a
-// single 16-byte store; record.w (the length, never 0) doubles as the "published" flag.  A consumer
-// warp reserves kDrainBatch positions with an atomicAdd on `head`, waits until they are published (or
-// until every producer has finished and the position is past `tail`), copies the records out and
-// zeroes them.  The oldest unconsumed position can always be written, so nobody waits in a circle.
+// Ring protocol (a bounded multi-producer multi-consumer queue with a sequence number per cell):
+// producers reserve positions with one atomicAdd on `tail` per warp and round; position p belongs to
+// cell p % kDefRing in lap p / kDefRing.  A cell's last word says whose turn it is:
+//     lap                       (bit 31 clear)  the cell is free and waits for the writer of that lap
+//     1<<31 | lap<<16 | len16   (bit 31 set)    the record of that lap is in the cell
+// so a writer that is a whole lap ahead waits for its turn instead of overwriting, and the record
+// is published by the same single 16-byte store that carries it.  A consumer warp reserves
+// kDrainBatch positions with an atomicAdd on `head`, waits until they are published (or until every
+// producer has finished and the position is past `tail`), copies the records out and hands the cells
+// to the next lap.  The oldest unconsumed position can always be written and read, so nobody waits
+// in a circle; both sides carry a watchdog that raises an error flag instead of hanging.
+// len16 saturates at 0xFFFF: the consumer then finds the word's start by scanning the text backwards.
 struct DefCtl { u32 tail, head, done, abort_flag; };
+
+__device__ __forceinline__ u32 ring_lap(u32 pos) { return (pos / kDefRing) & 0x7FFFu; }
+__device__ __forceinline__ u32 ring_full_word(u32 pos, u32 len) {
+    return 0x80000000u | (ring_lap(pos) << 16) | (len > 0xFFFFu ? 0xFFFFu : len);
+}
+
+// Length of the word that ends at buffer offset `end` (exclusive) when it is known to be >= 0xFFFF.
+__device__ __noinline__ u64 long_word_length(const uint8_t *buf, u64 end) {
+    u64 s = end;
+    while (s > 0) {
+        const u32 ch = buf[s - 1];
+        if (ch == 0x20 || ch == 0x0A || ch == 0x0D) break;
+        s--;
+    }
+    return end - s;
+}
 
 __device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
 
@@ -495,13 +525,13 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
                 if (live & (1u << j)) continue;
                 const u32 pos = b + lane + 32 * j;
                 const uint4 r = lds128_volatile(&ring[pos & (kDefRing - 1)]);
-                if (r.w != 0) {
+                if ((r.w >> 16) == (0x8000u | ring_lap(pos))) { // this position's record is in
                     rec[j] = r; live |= 1u << j;
-                    ring[pos & (kDefRing - 1)].w = 0; // the position may be reused
+                    ring[pos & (kDefRing - 1)].w = (ring_lap(pos) + 1) & 0x7FFFu; // the cell goes to the next lap
                 } else if (!(all_done && (int)(tail - pos) <= 0)) ok = false; // reserved but not yet written
             }
             if (__all_sync(0xFFFFFFFFu, ok)) { finished = all_done && (int)(tail - b) <= 0; break; }
-            if (++spins > (1u << 22)) { ctl->abort_flag = 1; atomicOr(&T.st->err, kErrRingTimeout); break; }
+            if (++spins > (1u << 25)) { ctl->abort_flag = 1; atomicOr(&T.st->err, kErrRingTimeout); break; }
             __nanosleep(40);
         }
         u32 slot[R]; ulonglong2 key[R]; u64 k1[R];
@@ -509,6 +539,8 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
 #pragma unroll
         for (int j = 0; j < R; j++) {
             if (!(live & (1u << j))) { rec[j] = make_uint4(0, 0, 0, 0); continue; }
+            rec[j].w &= 0xFFFFu; // the word's length (saturated)
+            if (rec[j].w == 0xFFFFu) rec[j].w = (u32)long_word_length(Lp->buf, cta_base + rec[j].z);
             const u32 len = rec[j].w;
             if (len <= 8) { // still room in the CTA's table?
                 const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
@@ -853,13 +885,14 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                         if (bl) {
                             u32 pos = 0;
                             if (lane == 0) pos = atomicAdd(&s_ctl.tail, (u32)__popc(bl));
-                            pos = (__shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bl & lt_mask)) & (kDefRing - 1);
+                            pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bl & lt_mask);
+                            const u32 cell = pos & (kDefRing - 1);
                             u32 spins = 0;
-                            while (__any_sync(0xFFFFFFFFu, dlong && reinterpret_cast<volatile uint4 *>(def_ring)[pos].w != 0)) {
-                                if (++spins > (1u << 22)) { s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break; }
+                            while (__any_sync(0xFFFFFFFFu, dlong && reinterpret_cast<volatile uint4 *>(def_ring)[cell].w != ring_lap(pos))) {
+                                if (++spins > (1u << 25)) { s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break; }
                                 __nanosleep(64);
                             }
-                            if (dlong) def_ring[pos] = make_uint4(klo, khi, relT + (u32)e, (u32)len);
+                            if (dlong) def_ring[cell] = make_uint4(klo, khi, relT + (u32)e, ring_full_word(pos, (u32)len));
                             n_long += dlong;
                         }
                         continue;
@@ -885,18 +918,19 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
 #endif
                     const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
                     if (bq) { // hand the misses and the 9+ byte words to the consumer warps
-                        u32 at = 0;
-                        if (lane == 0) at = atomicAdd(&s_ctl.tail, (u32)__popc(bq));
-                        at = (__shfl_sync(0xFFFFFFFFu, at, 0) + __popc(bq & lt_mask)) & (kDefRing - 1);
-                        u32 spins = 0;
-                        while (__any_sync(0xFFFFFFFFu, defer && reinterpret_cast<volatile uint4 *>(def_ring)[at].w != 0)) {
-                            if (++spins > (1u << 22) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag)) {
+                        u32 pos = 0;
+                        if (lane == 0) pos = atomicAdd(&s_ctl.tail, (u32)__popc(bq));
+                        pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bq & lt_mask);
+                        const u32 cell = pos & (kDefRing - 1);
+                        u32 spins = 0; // wait for the cell's turn (normally it is free already)
+                        while (__any_sync(0xFFFFFFFFu, defer && reinterpret_cast<volatile uint4 *>(def_ring)[cell].w != ring_lap(pos))) {
+                            if (++spins > (1u << 25) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag)) {
                                 s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break;
                             }
                             __nanosleep(64); // the ring is full: leave the issue slots to the consumers
                         }
 #ifndef WC_EXP_NODRAIN
-                        if (defer) def_ring[at] = make_uint4(klo, khi, rel, (u32)len);
+                        if (defer) def_ring[cell] = make_uint4(klo, khi, rel, ring_full_word(pos, (u32)len));
 #endif
                         n_long += defer && len > 8;
                     }
