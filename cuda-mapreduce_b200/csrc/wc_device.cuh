@@ -101,8 +101,8 @@ struct WarpSummary { // per warp, in input order: what finding P0 needs
 // that flushed it -- to be radix-sorted and run-length reduced at the end of the job.
 struct EmitBuf {
     u64 *cursor;       // records written so far (device counter); nullptr: hash path
-    u64 *hash;         // [cap] sort keys
-    u32 *idx;          // [cap] record index (the sort's payload)
+    u64 *hash;         // [cap] sort keys, filled in by wc_aggregate
+    u32 *idx;          // [cap] record index (the sort's payload), filled in by wc_aggregate
     ulonglong2 *key;   // [cap] the word, zero padded to 16 bytes
     u64 *end;          // [cap] absolute offset of the delimiter that flushed it
     u64 cap;
@@ -472,23 +472,12 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
 // producer has finished and the position is past `tail`), copies the records out and hands the cells
 // to the next lap.  The oldest unconsumed position can always be written and read, so nobody waits
 // in a circle; both sides carry a watchdog that raises an error flag instead of hanging.
-// len16 saturates at 0xFFFF: the consumer then finds the word's start by scanning the text backwards.
+// len16 saturates at 0xFFFF; records of 17+ byte words carry the full length in their first word.
 struct DefCtl { u32 tail, head, done, abort_flag; };
 
 __device__ __forceinline__ u32 ring_lap(u32 pos) { return (pos / kDefRing) & 0x7FFFu; }
 __device__ __forceinline__ u32 ring_full_word(u32 pos, u32 len) {
     return 0x80000000u | (ring_lap(pos) << 16) | (len > 0xFFFFu ? 0xFFFFu : len);
-}
-
-// Length of the word that ends at buffer offset `end` (exclusive) when it is known to be >= 0xFFFF.
-__device__ __noinline__ u64 long_word_length(const uint8_t *buf, u64 end) {
-    u64 s = end;
-    while (s > 0) {
-        const u32 ch = buf[s - 1];
-        if (ch == 0x20 || ch == 0x0A || ch == 0x0D) break;
-        s--;
-    }
-    return end - s;
 }
 
 __device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
@@ -539,8 +528,8 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
 #pragma unroll
         for (int j = 0; j < R; j++) {
             if (!(live & (1u << j))) { rec[j] = make_uint4(0, 0, 0, 0); continue; }
-            rec[j].w &= 0xFFFFu; // the word's length (saturated)
-            if (rec[j].w == 0xFFFFu) rec[j].w = (u32)long_word_length(Lp->buf, cta_base + rec[j].z);
+            rec[j].w &= 0xFFFFu;                 // the word's length, saturated at 0xFFFF ...
+            if (rec[j].w > 16) rec[j].w = rec[j].x; // ... a 17+ byte word carries its full length instead of its first bytes
             const u32 len = rec[j].w;
             if (len <= 8) { // still room in the CTA's table?
                 const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
@@ -874,9 +863,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                                     k1hi = __funnelshift_r(r[3], r[4], sh) & keep1.y;
                                 }
                                 const u64 k0 = (u64)klo | ((u64)khi << 32), k1 = (u64)k1lo | ((u64)k1hi << 32);
-                                L.em.hash[at] = mix64(k0 ^ mix64(k1 + 0x9E3779B97F4A7C15ull));
-                                L.em.idx[at] = (u32)at;
-                                L.em.key[at] = make_ulonglong2(k0, k1);
+                                L.em.key[at] = make_ulonglong2(k0, k1); // (sort keys are derived from these at the end)
                                 L.em.end[at] = L.base + T0 + (u64)e;
                             } else if (emit) atomicOr(&st->err, kErrEmitFull);
                         }
@@ -892,7 +879,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                                 if (++spins > (1u << 25)) { s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break; }
                                 __nanosleep(64);
                             }
-                            if (dlong) def_ring[cell] = make_uint4(klo, khi, relT + (u32)e, ring_full_word(pos, (u32)len));
+                            if (dlong) def_ring[cell] = make_uint4((u32)len, khi, relT + (u32)e, ring_full_word(pos, (u32)len));
                             n_long += dlong;
                         }
                         continue;
@@ -930,7 +917,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                             __nanosleep(64); // the ring is full: leave the issue slots to the consumers
                         }
 #ifndef WC_EXP_NODRAIN
-                        if (defer) def_ring[cell] = make_uint4(klo, khi, rel, ring_full_word(pos, (u32)len));
+                        if (defer) def_ring[cell] = make_uint4(len > 16 ? (u32)len : klo, khi, rel, ring_full_word(pos, (u32)len));
 #endif
                         n_long += defer && len > 8;
                     }

@@ -319,8 +319,6 @@ static int ensure_emit_capacity(wc_engine *e, size_t n) {
         CK(cudaMalloc((void **)&nb.key, cap * sizeof(ulonglong2)));
         CK(cudaMalloc((void **)&nb.end, cap * sizeof(u64)));
         if (have) {
-            CK(cudaMemcpy(nb.hash, e->em.hash, have * sizeof(u64), cudaMemcpyDeviceToDevice));
-            CK(cudaMemcpy(nb.idx, e->em.idx, have * sizeof(u32), cudaMemcpyDeviceToDevice));
             CK(cudaMemcpy(nb.key, e->em.key, have * sizeof(ulonglong2), cudaMemcpyDeviceToDevice));
             CK(cudaMemcpy(nb.end, e->em.end, have * sizeof(u64), cudaMemcpyDeviceToDevice));
         }
@@ -351,6 +349,7 @@ static int sort_aggregate(wc_engine *e, u64 stop_abs) {
     CK(cudaMalloc((void **)&flags, n * sizeof(u32)));
     CK(cudaMalloc((void **)&d_coll, sizeof(u64)));
     CK(cudaMemsetAsync(d_coll, 0, sizeof(u64), e->stream));
+    wc::sort_prepare_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(e->em.key, n, e->em.hash, e->em.idx);
     cub::DoubleBuffer<u64> dk(e->em.hash, hash_alt);
     cub::DoubleBuffer<u32> dv(e->em.idx, idx_alt);
     size_t tb_sort = 0, tb_scan = 0;
@@ -376,10 +375,7 @@ static int sort_aggregate(wc_engine *e, u64 stop_abs) {
                                                                       e->so_key, e->so_count, e->so_first);
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(e->stream));
-    // the sort may have left the records in the alternate buffers: make them the current ones
-    if (dk.Current() != e->em.hash) { std::swap(e->em.hash, hash_alt); }
-    if (dv.Current() != e->em.idx) { std::swap(e->em.idx, idx_alt); }
-    e->launches += 2;
+    e->launches += 3;
     e->so_runs = n_runs; e->so_coll = coll;
     cudaFree(hash_alt); cudaFree(idx_alt); cudaFree(flags); cudaFree(temp); cudaFree(d_coll);
     return WC_OK;

@@ -13,6 +13,15 @@
 namespace wc {
 
 // flags[i] = 1 iff sorted record i starts a run (its word differs from the previous record's)
+// sort key = 64-bit hash of the 16-byte word; payload = the record's index
+__global__ void sort_prepare_kernel(const ulonglong2 *key, u64 n, u64 *hash, u32 *idx) {
+    for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+        const ulonglong2 k = key[i];
+        hash[i] = mix64(k.x ^ mix64(k.y + 0x9E3779B97F4A7C15ull));
+        idx[i] = (u32)i;
+    }
+}
+
 // collisions: runs that start although the hash did not change (two different words, one hash) -- then
 // the same word may form more than one run and the host merges them.
 __global__ void sort_mark_heads_kernel(const u64 *hash, const u32 *idx, const ulonglong2 *key, u64 n, u32 *flags,
