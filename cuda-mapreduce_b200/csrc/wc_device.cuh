@@ -264,16 +264,17 @@ __device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u32 
 
 // -------------------------------------------------------- global long table (17+ bytes)
 
+// Very long words (the adversarial corpus has some of 1 MiB) are handled by one lane, so their loops
+// keep 16 independent 8-byte loads in flight per step: they are bound by load latency, not by arithmetic.
 __device__ __forceinline__ u64 long_hash(const uint8_t *buf, u64 start, u64 len) {
     u64 h = 0x9E3779B97F4A7C15ull ^ (len * 0xFF51AFD7ED558CCDull);
     u64 i = 0;
-    for (; i + 32 <= len; i += 32) { // four loads in flight per step: very long words are latency bound
-        const u64 a = load8_unaligned(buf, start + i), b = load8_unaligned(buf, start + i + 8);
-        const u64 c = load8_unaligned(buf, start + i + 16), d = load8_unaligned(buf, start + i + 24);
-        h = (h ^ a) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
-        h = (h ^ b) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
-        h = (h ^ c) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
-        h = (h ^ d) * 0x9FB21C651E98DF25ull; h ^= h >> 32;
+    for (; i + 128 <= len; i += 128) {
+        u64 v[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) v[j] = load8_unaligned(buf, start + i + 8 * j);
+#pragma unroll
+        for (int j = 0; j < 16; j++) { h = (h ^ v[j]) * 0x9FB21C651E98DF25ull; h ^= h >> 32; }
     }
     for (; i + 8 <= len; i += 8) {
         h = (h ^ load8_unaligned(buf, start + i)) * 0x9FB21C651E98DF25ull;
@@ -290,6 +291,15 @@ __device__ __forceinline__ u64 long_hash(const uint8_t *buf, u64 start, u64 len)
 __device__ __forceinline__ bool long_equal(const Tables &T, u64 unit, const uint8_t *buf, u64 start, u64 len) {
     if (__ldcg(&T.arena[unit]) != len) return false;
     u64 i = 0;
+    for (; i + 64 <= len; i += 64) {
+        u64 a[8], b[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) { a[j] = __ldcg(&T.arena[unit + 1 + (i >> 3) + j]); b[j] = load8_unaligned(buf, start + i + 8 * j); }
+        u64 diff = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) diff |= a[j] ^ b[j];
+        if (diff) return false;
+    }
     for (; i + 8 <= len; i += 8)
         if (__ldcg(&T.arena[unit + 1 + (i >> 3)]) != load8_unaligned(buf, start + i)) return false;
     if (i < len) {
@@ -319,6 +329,13 @@ __device__ __noinline__ u32 long_insert(const Tables *Tp, const uint8_t *buf, u6
                 if (idx + units > T.arena_units) { atomicOr(&T.st->err, kErrArenaFull); return 0; }
                 T.arena[idx] = len;
                 u64 i = 0;
+                for (; i + 128 <= len; i += 128) {
+                    u64 v[16];
+#pragma unroll
+                    for (int j = 0; j < 16; j++) v[j] = load8_unaligned(buf, start + i + 8 * j);
+#pragma unroll
+                    for (int j = 0; j < 16; j++) T.arena[idx + 1 + (i >> 3) + j] = v[j];
+                }
                 for (; i + 8 <= len; i += 8) T.arena[idx + 1 + (i >> 3)] = load8_unaligned(buf, start + i);
                 if (i < len) T.arena[idx + 1 + (i >> 3)] = load8_unaligned(buf, start + i, (u32)(len - i));
                 __threadfence();
@@ -465,22 +482,30 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
 // producers reserve positions with one atomicAdd on `tail` per warp and round; position p belongs to
 // cell p % kDefRing in lap p / kDefRing.  A cell's last word says whose turn it is:
 //     lap                       (bit 31 clear)  the cell is free and waits for the writer of that lap
-//     1<<31 | lap<<16 | len16   (bit 31 set)    the record of that lap is in the cell
+//     1<<31 | lap<<16 | t<<15 | len15  (bit 31 set)  the record of that lap is in the cell
 // so a writer that is a whole lap ahead waits for its turn instead of overwriting, and the record
 // is published by the same single 16-byte store that carries it.  A consumer warp reserves
 // kDrainBatch positions with an atomicAdd on `head`, waits until they are published (or until every
 // producer has finished and the position is past `tail`), copies the records out and hands the cells
 // to the next lap.  The oldest unconsumed position can always be written and read, so nobody waits
 // in a circle; both sides carry a watchdog that raises an error flag instead of hanging.
-// len16 saturates at 0xFFFF; records of 17+ byte words carry the full length in their first word.
+// len15 saturates; records of 17+ byte words carry the full length in their first word.  t: the
+// word's shared-memory slot already belongs to another word.
 struct DefCtl { u32 tail, head, done, abort_flag; };
 
 __device__ __forceinline__ u32 ring_lap(u32 pos) { return (pos / kDefRing) & 0x7FFFu; }
-__device__ __forceinline__ u32 ring_full_word(u32 pos, u32 len) {
-    return 0x80000000u | (ring_lap(pos) << 16) | (len > 0xFFFFu ? 0xFFFFu : len);
+// bit 15: the word's shared-memory slot was seen occupied by another word (no point in trying to claim it)
+__device__ __forceinline__ u32 ring_full_word(u32 pos, u32 len, bool slot_taken) {
+    return 0x80000000u | (ring_lap(pos) << 16) | (slot_taken ? 0x8000u : 0u) | (len > 0x7FFFu ? 0x7FFFu : len);
 }
 
 __device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ u32 atoms_add(u32 *p, u32 v) { // one lane's shared-memory atomicAdd, as written
+    u32 old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(smem_addr(p)), "r"(v) : "memory");
+    return old;
+}
 
 __device__ __forceinline__ uint4 lds128_volatile(const void *p) { // one 16-byte shared-memory read, never cached in registers
     uint4 v;
@@ -499,7 +524,7 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
     volatile DefCtl *vc = ctl;
     for (;;) {
         u32 b = 0;
-        if (lane == 0) b = atomicAdd(&ctl->head, (u32)kDrainBatch);
+        if (lane == 0) b = atoms_add(&ctl->head, (u32)kDrainBatch);
         b = __shfl_sync(0xFFFFFFFFu, b, 0);
         uint4 rec[R];
         u32 live = 0; // bit j: record j was taken
@@ -528,10 +553,12 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
 #pragma unroll
         for (int j = 0; j < R; j++) {
             if (!(live & (1u << j))) { rec[j] = make_uint4(0, 0, 0, 0); continue; }
-            rec[j].w &= 0xFFFFu;                 // the word's length, saturated at 0xFFFF ...
+            const bool slot_taken = (rec[j].w & 0x8000u) != 0;
+            rec[j].w &= 0x7FFFu;                 // the word's length, saturated ...
             if (rec[j].w > 16) rec[j].w = rec[j].x; // ... a 17+ byte word carries its full length instead of its first bytes
             const u32 len = rec[j].w;
-            if (len <= 8) { // still room in the CTA's table?
+            if (len <= 8 && slot_taken) { todo |= 1u << j; n_spill++; }
+            else if (len <= 8) { // the slot looked free: claim it (this is how the CTA's table fills up)
                 const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
                 const u32 sidx = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
                 const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[sidx]), 0ull, k0);
@@ -871,7 +898,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                         const u32 bl = __ballot_sync(0xFFFFFFFFu, dlong);
                         if (bl) {
                             u32 pos = 0;
-                            if (lane == 0) pos = atomicAdd(&s_ctl.tail, (u32)__popc(bl));
+                            if (lane == 0) pos = atoms_add(&s_ctl.tail, (u32)__popc(bl));
                             pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bl & lt_mask);
                             const u32 cell = pos & (kDefRing - 1);
                             u32 spins = 0;
@@ -879,7 +906,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                                 if (++spins > (1u << 25)) { s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break; }
                                 __nanosleep(64);
                             }
-                            if (dlong) def_ring[cell] = make_uint4((u32)len, khi, relT + (u32)e, ring_full_word(pos, (u32)len));
+                            if (dlong) def_ring[cell] = make_uint4((u32)len, khi, relT + (u32)e, ring_full_word(pos, (u32)len, false));
                             n_long += dlong;
                         }
                         continue;
@@ -906,7 +933,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
                     if (bq) { // hand the misses and the 9+ byte words to the consumer warps
                         u32 pos = 0;
-                        if (lane == 0) pos = atomicAdd(&s_ctl.tail, (u32)__popc(bq));
+                        if (lane == 0) pos = atoms_add(&s_ctl.tail, (u32)__popc(bq));
                         pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bq & lt_mask);
                         const u32 cell = pos & (kDefRing - 1);
                         u32 spins = 0; // wait for the cell's turn (normally it is free already)
@@ -917,7 +944,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                             __nanosleep(64); // the ring is full: leave the issue slots to the consumers
                         }
 #ifndef WC_EXP_NODRAIN
-                        if (defer) def_ring[cell] = make_uint4(len > 16 ? (u32)len : klo, khi, rel, ring_full_word(pos, (u32)len));
+                        if (defer) def_ring[cell] = make_uint4(len > 16 ? (u32)len : klo, khi, rel, ring_full_word(pos, (u32)len, (ent.x | ent.y) != 0));
 #endif
                         n_long += defer && len > 8;
                     }
