@@ -71,6 +71,7 @@ struct Status {
     u64 ovf_count;    // records appended to the overflow log (may exceed its capacity: then err is set)
     u32 p0_found;
     u32 err;
+    u64 dbg[8];       // WC_PROFILE builds: consumer cycles (wait, claim, global), batches; producer ring-full cycles, total
 };
 
 struct Tables {
@@ -220,29 +221,53 @@ __device__ __forceinline__ ulonglong2 cas128(ulonglong2 *addr, ulonglong2 cmp, u
     return old;
 }
 
-// Home slot of a word of 1..16 bytes in the global word table: a function of its first 8 bytes and
-// its length only, so that it is known before bytes 8..15 have been fetched.
+// The global word table is probed a BUCKET of four slots (64 bytes) at a time: all four keys are
+// read at once, so a lookup costs one memory round trip unless the whole bucket belongs to other
+// words (probability ~ load^4) -- with 64 lookups in flight per consumer warp, a scheme in which a
+// few percent of them need a second trip would make every batch wait for it.
+constexpr u32 kBucket = 4;
+struct Bucket { ulonglong2 k[kBucket]; };
+
+// Home bucket (its first slot) of a word of 1..16 bytes: a function of its first 8 bytes and its
+// length only, so that it is known before bytes 8..15 have been fetched.
 __device__ __forceinline__ u32 word_home(const Tables &T, u64 k0, u32 len) {
-    return hash_key128((u32)k0, (u32)(k0 >> 32), len, 0x5bd1e995u) >> (32 - T.w_log2);
+    return (hash_key128((u32)k0, (u32)(k0 >> 32), len, 0x5bd1e995u) >> (34 - T.w_log2)) * kBucket;
+}
+
+__device__ __forceinline__ Bucket load_bucket(const Tables &T, u32 slot) {
+    Bucket b;
+#pragma unroll
+    for (u32 i = 0; i < kBucket; i++) b.k[i] = __ldcg(&T.w_keys[slot + i]);
+    return b;
 }
 
 __device__ __forceinline__ u32 key_len8(u64 k0) { return 8u - ((u32)__clzll(k0) >> 3); } // bytes used, k0 != 0
 
 // Adds `delta` occurrences of a word of 1..16 bytes (k0 = bytes 0..7, k1 = bytes 8..15, zero padded)
-// to the global table, probing from `slot` whose key the caller has already loaded (`k`).
+// to the global table, starting at the bucket at `slot` whose keys the caller has already loaded.
 // Returns 1 if it claimed a new slot.
 __device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u64 delta, u64 first_abs, u32 slot,
-                                              ulonglong2 k) {
+                                              Bucket b) {
     const u32 mask = (u32)((1ull << T.w_log2) - 1);
     u32 is_new = 0;
     for (u32 probes = 0;; ++probes) {
-        if (k.x == 0) { // a used slot never has k.x == 0: a word's first byte is not 0x00
-            k = cas128(&T.w_keys[slot], make_ulonglong2(0, 0), make_ulonglong2(k0, k1));
-            if (k.x == 0) { is_new = 1; k.x = k0; k.y = k1; }
+        u32 found = kBucket;
+#pragma unroll
+        for (u32 i = 0; i < kBucket; i++)
+            if (found == kBucket && b.k[i].x == k0 && b.k[i].y == k1) found = i;
+        if (found == kBucket) {
+#pragma unroll
+            for (u32 i = 0; i < kBucket; i++) {
+                if (found != kBucket || b.k[i].x != 0) continue; // a used slot never has k.x == 0
+                const ulonglong2 old = cas128(&T.w_keys[slot + i], make_ulonglong2(0, 0), make_ulonglong2(k0, k1));
+                if (old.x == 0) { is_new = 1; found = i; }
+                else if (old.x == k0 && old.y == k1) found = i;
+                else b.k[i] = old; // somebody else's word got there first
+            }
         }
-        if (k.x == k0 && k.y == k1) break;
-        slot = (slot + 1) & mask;
-        if (probes >= kMaxWordProbes || probes >= mask) { // the table is too full here: defer to the host
+        if (found != kBucket) { slot += found; break; }
+        slot = (slot + kBucket) & mask;
+        if (probes >= kMaxWordProbes / kBucket || probes * kBucket >= mask) { // too full here: defer to the host
             const u64 at = atomicAdd(&T.st->ovf_count, 1ull);
             if (at < T.ovf_cap) {
                 T.ovf_log[4 * at] = k0; T.ovf_log[4 * at + 1] = k1;
@@ -250,7 +275,7 @@ __device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u
             } else atomicOr(&T.st->err, kErrWordFull);
             return 0;
         }
-        k = __ldcg(&T.w_keys[slot]);
+        b = load_bucket(T, slot);
     }
     atomicAdd(&T.w_counts[slot], delta); // both fire-and-forget (RED)
     atomicMax(&T.w_finv[slot], ~first_abs);
@@ -259,7 +284,7 @@ __device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u
 
 __device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u32 len, u64 delta, u64 first_abs) {
     const u32 slot = word_home(T, k0, len);
-    return word_insert_at(T, k0, k1, delta, first_abs, slot, __ldcg(&T.w_keys[slot]));
+    return word_insert_at(T, k0, k1, delta, first_abs, slot, load_bucket(T, slot));
 }
 
 // -------------------------------------------------------- global long table (17+ bytes)
@@ -522,6 +547,9 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
     constexpr int R = kDrainBatch / 32;
     u32 n_wnew = 0, n_xnew = 0, n_spill = 0;
     volatile DefCtl *vc = ctl;
+#ifdef WC_PROFILE
+    long long pc_wait = 0, pc_claim = 0, pc_glob = 0, pc_batches = 0, pc_t = clock64();
+#endif
     for (;;) {
         u32 b = 0;
         if (lane == 0) b = atoms_add(&ctl->head, (u32)kDrainBatch);
@@ -545,10 +573,13 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
                 } else if (!(all_done && (int)(tail - pos) <= 0)) ok = false; // reserved but not yet written
             }
             if (__all_sync(0xFFFFFFFFu, ok)) { finished = all_done && (int)(tail - b) <= 0; break; }
-            if (++spins > (1u << 25)) { ctl->abort_flag = 1; atomicOr(&T.st->err, kErrRingTimeout); break; }
-            __nanosleep(40);
+            if (++spins > (1u << 23)) { ctl->abort_flag = 1; atomicOr(&T.st->err, kErrRingTimeout); break; }
+            __nanosleep(spins < 4 ? 200 : 800); // a batch takes about a microsecond to fill: do not burn issue slots polling
         }
-        u32 slot[R]; ulonglong2 key[R]; u64 k1[R];
+#ifdef WC_PROFILE
+        { long long t = clock64(); pc_wait += t - pc_t; pc_t = t; pc_batches++; }
+#endif
+        u32 slot[R]; Bucket key[R]; u64 k1[R];
         u32 todo = 0; // bit j: record j goes to the global word table
 #pragma unroll
         for (int j = 0; j < R; j++) {
@@ -569,13 +600,16 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
                 } else { todo |= 1u << j; n_spill++; }
             } else if (len <= 16) todo |= 1u << j;
         }
+#ifdef WC_PROFILE
+        { long long t = clock64(); pc_claim += t - pc_t; pc_t = t; }
+#endif
 #pragma unroll
         for (int j = 0; j < R; j++) { // issue every global read of the batch ...
             const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-            slot[j] = 0; key[j] = make_ulonglong2(0, 0); k1[j] = 0;
+            slot[j] = 0; k1[j] = 0;
             if (todo & (1u << j)) {
                 slot[j] = word_home(T, k0, rec[j].w);
-                key[j] = __ldcg(&T.w_keys[slot[j]]);
+                key[j] = load_bucket(T, slot[j]);
                 if (rec[j].w > 8) k1[j] = load8_unaligned(Lp->buf, cta_base + rec[j].z - rec[j].w + 8, rec[j].w - 8);
             }
         }
@@ -586,8 +620,17 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
             if (todo & (1u << j)) n_wnew += word_insert_at(T, k0, k1[j], delta, Lp->base + end, slot[j], key[j]);
             else if (rec[j].w > 16) n_xnew += long_insert(Tp, Lp->buf, end - rec[j].w, rec[j].w, delta, Lp->base + end);
         }
+#ifdef WC_PROFILE
+        { long long t = clock64(); pc_glob += t - pc_t; pc_t = t; }
+#endif
         if (finished || vc->abort_flag) break;
     }
+#ifdef WC_PROFILE
+    if (lane == 0) {
+        atomicAdd(&T.st->dbg[0], (u64)pc_wait); atomicAdd(&T.st->dbg[1], (u64)pc_claim);
+        atomicAdd(&T.st->dbg[2], (u64)pc_glob); atomicAdd(&T.st->dbg[3], (u64)pc_batches);
+    }
+#endif
     n_wnew = __reduce_add_sync(0xFFFFFFFFu, n_wnew);
     n_xnew = __reduce_add_sync(0xFFFFFFFFu, n_xnew);
     n_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
@@ -937,12 +980,18 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                         pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bq & lt_mask);
                         const u32 cell = pos & (kDefRing - 1);
                         u32 spins = 0; // wait for the cell's turn (normally it is free already)
+#ifdef WC_PROFILE
+                        const long long pw0 = clock64();
+#endif
                         while (__any_sync(0xFFFFFFFFu, defer && reinterpret_cast<volatile uint4 *>(def_ring)[cell].w != ring_lap(pos))) {
                             if (++spins > (1u << 25) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag)) {
                                 s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break;
                             }
                             __nanosleep(64); // the ring is full: leave the issue slots to the consumers
                         }
+#ifdef WC_PROFILE
+                        if (lane == 0 && spins) atomicAdd(&st->dbg[4], (u64)(clock64() - pw0));
+#endif
 #ifndef WC_EXP_NODRAIN
                         if (defer) def_ring[cell] = make_uint4(len > 16 ? (u32)len : klo, khi, rel, ring_full_word(pos, (u32)len, (ent.x | ent.y) != 0));
 #endif

@@ -714,6 +714,15 @@ extern "C" int wc_debug_classify16(const uint8_t *bytes16, uint32_t *delim_mask,
 
 extern "C" uint32_t wc_debug_smem_entries(void) { return wc::kSmemEntries; }
 
+// WC_PROFILE builds: the cycle counters of the last job (call after wc_sync / wc_finish)
+extern "C" int wc_debug_counters(wc_engine *e, uint64_t *out8) {
+    if (!e || !out8) return WC_ERR_INVALID;
+    wc::Status st;
+    if (cudaMemcpy(&st, e->d_status, sizeof(st), cudaMemcpyDeviceToHost) != cudaSuccess) return WC_ERR_CUDA;
+    for (int i = 0; i < 8; i++) out8[i] = st.dbg[i];
+    return WC_OK;
+}
+
 extern "C" uint32_t wc_debug_smem_slot(uint64_t key) {
     return (uint32_t)(((uint64_t)wc::hash32((u32)key, (u32)(key >> 32)) * wc::kSmemEntries) >> 32);
 }
@@ -899,7 +908,7 @@ uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts) { return wc::k
 namespace {
 
 constexpr u32 kStaticMaxWarps = 4096; // 256 SMs x 16 warps: more than any sm_100 part has
-constexpr size_t kStaticStatusBytes = 256;
+constexpr size_t kStaticStatusBytes = 512;
 constexpr size_t kStaticScratchBytes = kStaticStatusBytes + sizeof(wc::WarpSummary) * kStaticMaxWarps;
 static_assert(sizeof(wc::Status) <= kStaticStatusBytes, "Status must fit its slot");
 

@@ -244,6 +244,7 @@ WC_API int wc_debug_classify16(const uint8_t *bytes16, uint32_t *delim_mask, uin
                                uint32_t *kill_mask);
 WC_API uint32_t wc_debug_smem_slot(uint64_t key);
 WC_API uint32_t wc_debug_smem_entries(void);
+WC_API int wc_debug_counters(wc_engine *e, uint64_t *out8); /* cycle counters of -DWC_PROFILE builds */
 
 #ifdef __cplusplus
 }
