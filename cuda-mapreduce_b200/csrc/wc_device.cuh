@@ -193,6 +193,49 @@ __device__ __forceinline__ u64 warp_sum64(u64 v) {
     return v;
 }
 
+// ---- atomics with the address space spelled out.  Inside non-inlined device functions the compiler
+// only sees generic pointers: it then emits returning generic atomics (a memory round trip each) and
+// a run-time dispatch for shared memory.  These are what the code means.
+__device__ __forceinline__ void red_add_u64(u64 *p, u64 v) { // global, fire and forget
+    asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_max_u64(u64 *p, u64 v) {
+    asm volatile("red.global.max.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_or_u32(u32 *p, u32 v) {
+    asm volatile("red.global.or.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ u64 atom_add_u64(u64 *p, u64 v) { // global, returns the old value
+    u64 old;
+    asm volatile("atom.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ u64 atom_cas_u64(u64 *p, u64 cmp, u64 val) {
+    u64 old;
+    asm volatile("atom.global.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "l"(p), "l"(cmp), "l"(val) : "memory");
+    return old;
+}
+__device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ u64 atoms_cas_u64(void *p, u64 cmp, u64 val) { // shared
+    u64 old;
+    asm volatile("atom.shared.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "r"(smem_addr(p)), "l"(cmp), "l"(val) : "memory");
+    return old;
+}
+__device__ __forceinline__ void reds_add_u32(void *p, u32 v) {
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(smem_addr(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void reds_min_u32(void *p, u32 v) {
+    asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(smem_addr(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts_u32(void *p, u32 v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_addr(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ u32 lds_volatile_u32(const void *p) {
+    u32 v;
+    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_addr(p)) : "memory");
+    return v;
+}
+
 // ------------------------------------------------------- global word table (1..16 bytes)
 
 __host__ __device__ __forceinline__ u32 hash_key128(u32 a, u32 b, u32 c, u32 d) {
@@ -225,13 +268,18 @@ __device__ __forceinline__ ulonglong2 cas128(ulonglong2 *addr, ulonglong2 cmp, u
 // read at once, so a lookup costs one memory round trip unless the whole bucket belongs to other
 // words (probability ~ load^4) -- with 64 lookups in flight per consumer warp, a scheme in which a
 // few percent of them need a second trip would make every batch wait for it.
-constexpr u32 kBucket = 4;
+#ifndef WC_BUCKET
+#define WC_BUCKET 1
+#endif
+constexpr u32 kBucket = WC_BUCKET; // 1, 2 or 4
+constexpr u32 kBucketLog2 = kBucket == 4 ? 2 : kBucket == 2 ? 1 : 0;
+static_assert(kBucket == 1u << kBucketLog2, "bucket size");
 struct Bucket { ulonglong2 k[kBucket]; };
 
 // Home bucket (its first slot) of a word of 1..16 bytes: a function of its first 8 bytes and its
 // length only, so that it is known before bytes 8..15 have been fetched.
 __device__ __forceinline__ u32 word_home(const Tables &T, u64 k0, u32 len) {
-    return (hash_key128((u32)k0, (u32)(k0 >> 32), len, 0x5bd1e995u) >> (34 - T.w_log2)) * kBucket;
+    return (hash_key128((u32)k0, (u32)(k0 >> 32), len, 0x5bd1e995u) >> (32 + kBucketLog2 - T.w_log2)) * kBucket;
 }
 
 __device__ __forceinline__ Bucket load_bucket(const Tables &T, u32 slot) {
@@ -268,17 +316,17 @@ __device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u
         if (found != kBucket) { slot += found; break; }
         slot = (slot + kBucket) & mask;
         if (probes >= kMaxWordProbes / kBucket || probes * kBucket >= mask) { // too full here: defer to the host
-            const u64 at = atomicAdd(&T.st->ovf_count, 1ull);
+            const u64 at = atom_add_u64(&T.st->ovf_count, 1ull);
             if (at < T.ovf_cap) {
                 T.ovf_log[4 * at] = k0; T.ovf_log[4 * at + 1] = k1;
                 T.ovf_log[4 * at + 2] = delta; T.ovf_log[4 * at + 3] = first_abs;
-            } else atomicOr(&T.st->err, kErrWordFull);
+            } else red_or_u32(&T.st->err, kErrWordFull);
             return 0;
         }
         b = load_bucket(T, slot);
     }
-    atomicAdd(&T.w_counts[slot], delta); // both fire-and-forget (RED)
-    atomicMax(&T.w_finv[slot], ~first_abs);
+    red_add_u64(&T.w_counts[slot], delta); // both fire-and-forget
+    red_max_u64(&T.w_finv[slot], ~first_abs);
     return is_new;
 }
 
@@ -350,8 +398,8 @@ __device__ __noinline__ u32 long_insert(const Tables *Tp, const uint8_t *buf, u6
         if (r == 0) {
             if (my_ref == 0) {
                 u64 units = 1 + ((len + 7) >> 3);
-                u64 idx = atomicAdd(&T.st->arena_used, units);
-                if (idx + units > T.arena_units) { atomicOr(&T.st->err, kErrArenaFull); return 0; }
+                u64 idx = atom_add_u64(&T.st->arena_used, units);
+                if (idx + units > T.arena_units) { red_or_u32(&T.st->err, kErrArenaFull); return 0; }
                 T.arena[idx] = len;
                 u64 i = 0;
                 for (; i + 128 <= len; i += 128) {
@@ -366,15 +414,15 @@ __device__ __noinline__ u32 long_insert(const Tables *Tp, const uint8_t *buf, u6
                 __threadfence();
                 my_ref = (tag << 40) | idx;
             }
-            r = atomicCAS(&T.x_refs[slot], 0ull, my_ref);
+            r = atom_cas_u64(&T.x_refs[slot], 0ull, my_ref);
             if (r == 0) { is_new = 1; break; }
         }
         if ((r >> 40) == tag && long_equal(T, r & ((1ull << 40) - 1), buf, start, len)) break;
         slot = (slot + 1) & mask;
-        if (probes > 4096 || probes >= mask) { atomicOr(&T.st->err, kErrLongFull); return 0; }
+        if (probes > 4096 || probes >= mask) { red_or_u32(&T.st->err, kErrLongFull); return 0; }
     }
-    atomicAdd(&T.x_counts[slot], delta);
-    atomicMax(&T.x_finv[slot], ~first_abs);
+    red_add_u64(&T.x_counts[slot], delta);
+    red_max_u64(&T.x_finv[slot], ~first_abs);
     return is_new;
 }
 
@@ -524,8 +572,6 @@ __device__ __forceinline__ u32 ring_full_word(u32 pos, u32 len, bool slot_taken)
     return 0x80000000u | (ring_lap(pos) << 16) | (slot_taken ? 0x8000u : 0u) | (len > 0x7FFFu ? 0x7FFFu : len);
 }
 
-__device__ __forceinline__ u32 smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
-
 __device__ __forceinline__ u32 atoms_add(u32 *p, u32 v) { // one lane's shared-memory atomicAdd, as written
     u32 old;
     asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(smem_addr(p)), "r"(v) : "memory");
@@ -539,14 +585,18 @@ __device__ __forceinline__ uint4 lds128_volatile(const void *p) { // one 16-byte
     return v;
 }
 
-__device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *Tp,
+#ifdef WC_EXP_NOINLINE
+__device__ __noinline__
+#else
+__device__ __forceinline__
+#endif
+void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *Tp,
                                               u64 cta_base, uint4 *tab) {
     const u32 lane = lane_id();
     const Tables &T = *Tp;
     const u64 delta = Lp->negate ? ~0ull : 1ull;
     constexpr int R = kDrainBatch / 32;
     u32 n_wnew = 0, n_xnew = 0, n_spill = 0;
-    volatile DefCtl *vc = ctl;
 #ifdef WC_PROFILE
     long long pc_wait = 0, pc_claim = 0, pc_glob = 0, pc_batches = 0, pc_t = clock64();
 #endif
@@ -558,9 +608,21 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
         u32 live = 0; // bit j: record j was taken
         u32 spins = 0;
         bool finished = false;
-        for (;;) { // wait for the batch
-            const bool all_done = vc->done == (u32)kProducers; // read before tail: tail is final once this holds
-            const u32 tail = vc->tail;
+        // Cells fill roughly in order: watch the batch's last cell only (one broadcast read per poll) and
+        // look at all of them once that one is in, or once every producer has finished.
+#ifndef WC_EXP_NOPREWAIT
+        __syncwarp();
+        for (const u32 last = b + kDrainBatch - 1;;) {
+            if ((lds_volatile_u32(&ring[last & (kDefRing - 1)].w) >> 16) == (0x8000u | ring_lap(last))) break;
+            if (lds_volatile_u32(&ctl->done) == (u32)kProducers || ++spins > (1u << 23)) break;
+            __nanosleep(spins < 4 ? 200 : 800); // a batch takes about a microsecond to fill: do not burn issue slots polling
+        }
+#endif
+        u32 polls = spins > (1u << 23) ? spins : 0; // (counted per pass of this loop, which the vote below keeps in step)
+        polls = __shfl_sync(0xFFFFFFFFu, polls, 0);
+        for (;;) { // take the batch
+            const bool all_done = lds_volatile_u32(&ctl->done) == (u32)kProducers; // read before tail: tail is final once this holds
+            const u32 tail = lds_volatile_u32(&ctl->tail);
             bool ok = true;
 #pragma unroll
             for (int j = 0; j < R; j++) {
@@ -569,12 +631,17 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
                 const uint4 r = lds128_volatile(&ring[pos & (kDefRing - 1)]);
                 if ((r.w >> 16) == (0x8000u | ring_lap(pos))) { // this position's record is in
                     rec[j] = r; live |= 1u << j;
-                    ring[pos & (kDefRing - 1)].w = (ring_lap(pos) + 1) & 0x7FFFu; // the cell goes to the next lap
+                    sts_u32(&ring[pos & (kDefRing - 1)].w, (ring_lap(pos) + 1) & 0x7FFFu); // the cell goes to the next lap
                 } else if (!(all_done && (int)(tail - pos) <= 0)) ok = false; // reserved but not yet written
             }
-            if (__all_sync(0xFFFFFFFFu, ok)) { finished = all_done && (int)(tail - b) <= 0; break; }
-            if (++spins > (1u << 23)) { ctl->abort_flag = 1; atomicOr(&T.st->err, kErrRingTimeout); break; }
-            __nanosleep(spins < 4 ? 200 : 800); // a batch takes about a microsecond to fill: do not burn issue slots polling
+            if (__all_sync(0xFFFFFFFFu, ok)) {
+                // lane 0's view decides for the warp: lanes that read `done` at different moments must
+                // not disagree about leaving the loop (the next __shfl_sync would wait for ever)
+                finished = __shfl_sync(0xFFFFFFFFu, (u32)(all_done && (int)(tail - b) <= 0), 0) != 0;
+                break;
+            }
+            if (++polls > (1u << 23)) { sts_u32(&ctl->abort_flag, 1); red_or_u32(&T.st->err, kErrRingTimeout); break; }
+            __nanosleep(200);
         }
 #ifdef WC_PROFILE
         { long long t = clock64(); pc_wait += t - pc_t; pc_t = t; pc_batches++; }
@@ -592,11 +659,11 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
             else if (len <= 8) { // the slot looked free: claim it (this is how the CTA's table fills up)
                 const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
                 const u32 sidx = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
-                const u64 old = atomicCAS(reinterpret_cast<u64 *>(&tab[sidx]), 0ull, k0);
+                const u64 old = atoms_cas_u64(&tab[sidx], 0ull, k0);
                 if (old == 0 || old == k0) {
                     u32 *cell = reinterpret_cast<u32 *>(&tab[sidx]);
-                    atomicAdd(cell + 2, (u32)delta);
-                    atomicMin(cell + 3, rec[j].z);
+                    reds_add_u32(cell + 2, (u32)delta);
+                    reds_min_u32(cell + 3, rec[j].z);
                 } else { todo |= 1u << j; n_spill++; }
             } else if (len <= 16) todo |= 1u << j;
         }
@@ -618,12 +685,26 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
             const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
             const u64 end = cta_base + rec[j].z; // buffer-relative offset of the delimiter
             if (todo & (1u << j)) n_wnew += word_insert_at(T, k0, k1[j], delta, Lp->base + end, slot[j], key[j]);
-            else if (rec[j].w > 16) n_xnew += long_insert(Tp, Lp->buf, end - rec[j].w, rec[j].w, delta, Lp->base + end);
+        }
+        // 17+ byte words last and on their own: a function call between the loads above and their use
+        // would push every loaded key through the stack.
+        u32 has_long = 0;
+#pragma unroll
+        for (int j = 0; j < R; j++) has_long |= rec[j].w > 16 ? 1u << j : 0u;
+        if (__any_sync(0xFFFFFFFFu, has_long != 0)) {
+#pragma unroll 1
+            for (int j = 0; j < R; j++) {
+                uint4 r = rec[0];
+#pragma unroll
+                for (int q = 1; q < R; q++) if (q == j) r = rec[q];
+                const u64 end = cta_base + r.z;
+                if (r.w > 16) n_xnew += long_insert(Tp, Lp->buf, end - r.w, r.w, delta, Lp->base + end);
+            }
         }
 #ifdef WC_PROFILE
         { long long t = clock64(); pc_glob += t - pc_t; pc_t = t; }
 #endif
-        if (finished || vc->abort_flag) break;
+        if (__any_sync(0xFFFFFFFFu, finished || lds_volatile_u32(&ctl->abort_flag) != 0)) break;
     }
 #ifdef WC_PROFILE
     if (lane == 0) {
@@ -635,9 +716,9 @@ __device__ __noinline__ void consume_deferred(uint4 *ring, DefCtl *ctl, const La
     n_xnew = __reduce_add_sync(0xFFFFFFFFu, n_xnew);
     n_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
     if (lane == 0) {
-        if (n_wnew) atomicAdd(&T.st->w_entries, (u64)n_wnew);
-        if (n_xnew) atomicAdd(&T.st->x_entries, (u64)n_xnew);
-        if (n_spill && !Lp->negate) atomicAdd(&T.st->n_spill, (u64)n_spill);
+        if (n_wnew) red_add_u64(&T.st->w_entries, (u64)n_wnew);
+        if (n_xnew) red_add_u64(&T.st->x_entries, (u64)n_xnew);
+        if (n_spill && !Lp->negate) red_add_u64(&T.st->n_spill, (u64)n_spill);
     }
 }
 
@@ -946,7 +1027,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                             const u32 cell = pos & (kDefRing - 1);
                             u32 spins = 0;
                             while (__any_sync(0xFFFFFFFFu, dlong && reinterpret_cast<volatile uint4 *>(def_ring)[cell].w != ring_lap(pos))) {
-                                if (++spins > (1u << 25)) { s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break; }
+                                if (__any_sync(0xFFFFFFFFu, ++spins > (1u << 25))) { s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break; }
                                 __nanosleep(64);
                             }
                             if (dlong) def_ring[cell] = make_uint4((u32)len, khi, relT + (u32)e, ring_full_word(pos, (u32)len, false));
@@ -984,7 +1065,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                         const long long pw0 = clock64();
 #endif
                         while (__any_sync(0xFFFFFFFFu, defer && reinterpret_cast<volatile uint4 *>(def_ring)[cell].w != ring_lap(pos))) {
-                            if (++spins > (1u << 25) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag)) {
+                            if (__any_sync(0xFFFFFFFFu, ++spins > (1u << 25) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag))) {
                                 s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break;
                             }
                             __nanosleep(64); // the ring is full: leave the issue slots to the consumers

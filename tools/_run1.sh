@@ -1,0 +1,2 @@
+for i in 1 2; do timeout 200 python -m pytest tests -m gpu -x -q 2>&1 | tail -2; done
+python bench.py --no-cpu-baseline --no-e2e --steps 10 --warmup 3 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('default', d['value'], d['ms_per_step'])"

@@ -39,6 +39,7 @@ def main():
     base = None
     agg = {}
     tot_inst = tot_samp = 0
+    dump = open(os.environ["NCU_DUMP"], "w") if os.environ.get("NCU_DUMP") else None  # per-instruction listing
     for r in rows[2:]:
         if len(r) < len(hdr):
             continue
@@ -51,6 +52,8 @@ def main():
         samp = int(r[col["# Samples"]] or 0)
         wf = int(r[col["L1 Wavefronts Shared"]] or 0)
         long_sb = int(r[col["stall_long_sb"]] or 0)
+        if dump:
+            dump.write("%05x %-22s %10d %6d %8d %6d  %s\n" % (off, "%s:%d" % line if line else "?", inst, samp, wf, long_sb, sass))
         a = agg.setdefault(line, [0, 0, 0, 0])
         a[0] += inst; a[1] += samp; a[2] += wf; a[3] += long_sb
         tot_inst += inst; tot_samp += samp
