@@ -22,7 +22,7 @@ typedef unsigned int u32;
 #define WC_WARPS 24
 #endif
 #ifndef WC_CONSUMERS
-#define WC_CONSUMERS 8
+#define WC_CONSUMERS 6
 #endif
 #ifndef WC_DRAIN
 #define WC_DRAIN 64
@@ -42,7 +42,9 @@ constexpr u32 kDefRing = 1024;             // per CTA: ring of deferred-word rec
 constexpr u64 kNone = ~0ull;
 constexpr u32 kMaxWordProbes = 128;        // longer probe chains in the global word table mean: grow it
 
-constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes;
+constexpr u32 kStageCap = 64;              // per producer warp: deferred records gathered before they go to the ring
+constexpr int kStageBytes = kStageCap * 16;
+constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kStageBytes;
 constexpr size_t kDefRingBytes = (size_t)kDefRing * 16;
 constexpr u32 kSmemEntries = (u32)((232448 - 256 - kDefRingBytes - kProducers * kWarpSmemBytes) / 16) & ~31u;
 constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16; // the per-CTA table gets what is left
@@ -585,6 +587,45 @@ __device__ __forceinline__ uint4 lds128_volatile(const void *p) { // one 16-byte
     return v;
 }
 
+// Moves a producer warp's n staged records (n <= kStageCap) to the CTA's ring: one reservation for
+// all of them, then each lane waits for its cell's turn (normally free already) and writes the
+// record with the position's lap number in its last word.  Staged w = len15 | slot_taken << 15.
+__device__ __forceinline__ void flush_stage(const uint4 *stage, u32 n, uint4 *ring, DefCtl *ctl, Status *st) {
+    const u32 lane = lane_id();
+    u32 pos0 = 0;
+    if (lane == 0) pos0 = atoms_add(&ctl->tail, n);
+    pos0 = __shfl_sync(0xFFFFFFFFu, pos0, 0);
+#ifdef WC_PROFILE
+    const long long pw0 = clock64();
+    bool waited = false;
+#endif
+    for (u32 i0 = 0; i0 < n; i0 += 32) {
+        const u32 i = i0 + lane;
+        const bool mine = i < n;
+        const u32 pos = pos0 + i, cell = pos & (kDefRing - 1);
+        uint4 r = make_uint4(0, 0, 0, 0);
+        if (mine) r = stage[i];
+        u32 spins = 0;
+        while (__any_sync(0xFFFFFFFFu, mine && lds_volatile_u32(&ring[cell].w) != ring_lap(pos))) {
+            if (__any_sync(0xFFFFFFFFu, ++spins > (1u << 25) || lds_volatile_u32(&ctl->abort_flag) != 0)) {
+                sts_u32(&ctl->abort_flag, 1); atomicOr(&st->err, kErrRingTimeout); break;
+            }
+#ifdef WC_PROFILE
+            waited = true;
+#endif
+            __nanosleep(64); // the ring is full: leave the issue slots to the consumers
+        }
+        r.w |= 0x80000000u | (ring_lap(pos) << 16);
+#ifndef WC_EXP_NODRAIN
+        if (mine) ring[cell] = r;
+#endif
+    }
+#ifdef WC_PROFILE
+    if (lane == 0 && waited) atomicAdd(&st->dbg[4], (u64)(clock64() - pw0));
+#endif
+    __syncwarp(); // the staged records have been read: the area may be overwritten
+}
+
 #ifdef WC_EXP_NOINLINE
 __device__ __noinline__
 #else
@@ -809,6 +850,8 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     // per-warp shared memory: [two tile buffers] [delimiter list]
     unsigned char *wbase = warp_all + warp * kWarpSmemBytes;
     unsigned short *dl = reinterpret_cast<unsigned short *>(wbase + kRingBytes);
+    uint4 *stage = reinterpret_cast<uint4 *>(wbase + kRingBytes + kDlBytes);
+    u32 n_staged = 0; // warp-uniform
 
     const u32 tiles_total = (u32)((L.n + kTile - 1) / kTile);
     const u32 gwarp = blockIdx.x * kProducers + warp;
@@ -1055,28 +1098,18 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const bool defer = word && !hit;
 #endif
                     const u32 bq = __ballot_sync(0xFFFFFFFFu, defer);
-                    if (bq) { // hand the misses and the 9+ byte words to the consumer warps
-                        u32 pos = 0;
-                        if (lane == 0) pos = atoms_add(&s_ctl.tail, (u32)__popc(bq));
-                        pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(bq & lt_mask);
-                        const u32 cell = pos & (kDefRing - 1);
-                        u32 spins = 0; // wait for the cell's turn (normally it is free already)
-#ifdef WC_PROFILE
-                        const long long pw0 = clock64();
-#endif
-                        while (__any_sync(0xFFFFFFFFu, defer && reinterpret_cast<volatile uint4 *>(def_ring)[cell].w != ring_lap(pos))) {
-                            if (__any_sync(0xFFFFFFFFu, ++spins > (1u << 25) || *reinterpret_cast<volatile u32 *>(&s_ctl.abort_flag))) {
-                                s_ctl.abort_flag = 1; atomicOr(&st->err, kErrRingTimeout); break;
-                            }
-                            __nanosleep(64); // the ring is full: leave the issue slots to the consumers
-                        }
-#ifdef WC_PROFILE
-                        if (lane == 0 && spins) atomicAdd(&st->dbg[4], (u64)(clock64() - pw0));
-#endif
-#ifndef WC_EXP_NODRAIN
-                        if (defer) def_ring[cell] = make_uint4(len > 16 ? (u32)len : klo, khi, rel, ring_full_word(pos, (u32)len, (ent.x | ent.y) != 0));
-#endif
+                    if (bq) { // stage the misses and the 9+ byte words; full stages go to the consumer warps' ring
+                        if (defer)
+                            stage[n_staged + __popc(bq & lt_mask)] =
+                                make_uint4(len > 16 ? (u32)len : klo, khi, rel,
+                                           ((u32)len > 0x7FFFu ? 0x7FFFu : (u32)len) | ((ent.x | ent.y) != 0 ? 0x8000u : 0u));
+                        n_staged += __popc(bq);
                         n_long += defer && len > 8;
+                        if (n_staged > kStageCap - 32) { // the next round might not fit
+                            __syncwarp();
+                            flush_stage(stage, n_staged, def_ring, &s_ctl, st);
+                            n_staged = 0;
+                        }
                     }
                 }
                 if (total > 0) first_prev = (int)(dl[total - 1] & 0x3FFu);
@@ -1104,6 +1137,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     }
 
     __syncwarp();
+    if (n_staged) flush_stage(stage, n_staged, def_ring, &s_ctl, st);
     if (lane == 0) atomicAdd(&s_ctl.done, 1u); // this producer will append nothing more
     } // producer warps
 

@@ -16,6 +16,7 @@
 #include "wc_shuffle.cuh"
 #include "wc_sort.cuh"
 #include <cub/cub.cuh>
+#include <chrono>
 #include <unordered_map>
 #include "wc_finalize.h"
 
@@ -56,6 +57,10 @@ struct wc_engine {
     u64 *d_ovf = nullptr;       // overflow log (wc::Tables::ovf_log)
     u64 ovf_cap = 0;
     u64 *d_cursors = nullptr;   // shuffle: per-partition counts / cursors (2 * kMaxParts + 2 words)
+    void *d_fin = nullptr, *h_fin = nullptr; // wc_finish: the used table entries, compacted (device / pinned host)
+    size_t d_fin_cap = 0, h_fin_cap = 0;
+    void *d_ord = nullptr;                   // wc_finish: sort keys and cub scratch
+    size_t d_ord_cap = 0;
     bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
     u64 job_bytes = 0;
 
@@ -83,6 +88,8 @@ struct wc_engine {
     } while (0)
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+namespace { constexpr u32 kMaxParts = 64; }
+static int ensure_cursors(wc_engine *e);
 
 // ----------------------------------------------------------------- tables
 
@@ -159,6 +166,9 @@ void wc_destroy(wc_engine *e) {
     if (e->d_status) cudaFree(e->d_status);
     if (e->d_ws) cudaFree(e->d_ws);
     if (e->d_cursors) cudaFree(e->d_cursors);
+    if (e->d_fin) cudaFree(e->d_fin);
+    if (e->d_ord) cudaFree(e->d_ord);
+    if (e->h_fin) cudaFreeHost(e->h_fin);
     if (e->so_key) { cudaFree(e->so_key); cudaFree(e->so_count); cudaFree(e->so_first); }
     if (e->em.cursor) cudaFree(e->em.cursor);
     if (e->em.hash) cudaFree(e->em.hash);
@@ -620,12 +630,17 @@ int wc_finish(wc_engine *e, wc_result **out) {
     if (!e || !out) return WC_ERR_INVALID;
     *out = nullptr;
     CK(cudaSetDevice(e->device));
+    static const bool timing = getenv("WC_TIMING") != nullptr; // stderr: where wc_finish spends its time
+    const auto t0 = std::chrono::steady_clock::now();
+    auto since = [&t0] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
     int rc = wc_end_input(e);
     if (rc != WC_OK) return rc;
     rc = wc_sync(e);
     if (rc != WC_OK) return rc;
+    const double t_sync = since();
     rc = settle_tables(e);
     if (rc != WC_OK) return rc;
+    const double t_settle = since();
     e->carry.clear();
     const wc::Status st = *e->h_status;
     if (st.err) {
@@ -636,43 +651,117 @@ int wc_finish(wc_engine *e, wc_result **out) {
         return WC_ERR_TABLE_FULL;
     }
 
-    // ---- bring the tables to the host
-    const size_t s_n = (size_t)1 << e->T.w_log2, l_n = (size_t)1 << e->T.x_log2;
-    std::vector<u64> tab((4 * s_n + 3 * l_n));
-    CK(cudaMemcpyAsync(tab.data(), e->table_block, tab.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
-    std::vector<u64> arena((size_t)st.arena_used);
-    if (st.arena_used > 1)
-        CK(cudaMemcpyAsync(arena.data(), e->T.arena, arena.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    // ---- bring the USED table entries to the host: compacted on the device into 32-byte records
+    // (the same kernels the multi-GPU exchange exports with), then one copy into pinned memory.
+    // The tables themselves can be tens of MB; the entries are a few.
+    const size_t n_w_max = (size_t)st.w_entries, n_x_max = (size_t)st.x_entries;
+    const size_t blob_max = (size_t)st.arena_used * 8;
+    const size_t n_ord = e->sort_mode ? 0 : n_w_max + n_x_max; // (sort mode adds its entries on the host: no device order)
+    const size_t off_w = 64, off_x = off_w + n_w_max * sizeof(wc::WordRecord),
+                 off_b = off_x + n_x_max * sizeof(wc::LongRecord), off_pk = off_b + blob_max,
+                 off_pf = off_pk + align_up(n_ord * sizeof(u32), 8), need = off_pf + align_up(n_ord * sizeof(u32), 8);
+    rc = ensure_cursors(e);
+    if (rc != WC_OK) return rc;
+    if (need > e->d_fin_cap) {
+        if (e->d_fin) cudaFree(e->d_fin);
+        e->d_fin = nullptr; e->d_fin_cap = 0;
+        CK(cudaMalloc(&e->d_fin, need + need / 4));
+        e->d_fin_cap = need + need / 4;
+    }
+    if (need > e->h_fin_cap) {
+        if (e->h_fin) cudaFreeHost(e->h_fin);
+        e->h_fin = nullptr; e->h_fin_cap = 0;
+        CK(cudaMallocHost(&e->h_fin, need + need / 4));
+        e->h_fin_cap = need + need / 4;
+    }
+    uint8_t *dfin = (uint8_t *)e->d_fin, *hfin = (uint8_t *)e->h_fin;
+    CK(cudaMemsetAsync(e->d_cursors, 0, (2 * kMaxParts + 2) * sizeof(u64), e->stream)); // offsets[0] = 0, cursors = 0
+    if (n_w_max)
+        wc::export_scatter_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, 1, e->d_cursors, e->d_cursors + kMaxParts,
+                                                                        (wc::WordRecord *)(dfin + off_w));
+    if (n_x_max)
+        wc::export_long_kernel<<<e->num_sms, 256, 0, e->stream>>>(e->T, e->d_cursors + 2 * kMaxParts,
+                                                                 (wc::LongRecord *)(dfin + off_x), (u64 *)(dfin + off_b));
+    CK(cudaGetLastError());
+    e->launches += (n_w_max != 0) + (n_x_max != 0);
+    if (n_ord > 1) {
+        // Two orders of the records for the host reduce, computed here where sorting is cheap: by the
+        // word's first 16 bytes (two stable radix passes: low half, then high half) and by first offset.
+        if (n_ord >= 0x7FFFFFF0ull) { e->err = "too many distinct words for wc_finish"; return WC_ERR_TOO_LARGE; }
+        const int n = (int)n_ord;
+        size_t tb = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, tb, (const u64 *)nullptr, (u64 *)nullptr, (const u32 *)nullptr,
+                                           (u32 *)nullptr, n, 0, 64, e->stream));
+        const size_t a8 = align_up(n_ord * sizeof(u64), 256), a4 = align_up(n_ord * sizeof(u32), 256);
+        const size_t need_ord = 5 * a8 + 2 * a4 + align_up(tb, 256);
+        if (need_ord > e->d_ord_cap) {
+            if (e->d_ord) cudaFree(e->d_ord);
+            e->d_ord = nullptr; e->d_ord_cap = 0;
+            CK(cudaMalloc(&e->d_ord, need_ord + need_ord / 4));
+            e->d_ord_cap = need_ord + need_ord / 4;
+        }
+        uint8_t *q = (uint8_t *)e->d_ord;
+        u64 *hi = (u64 *)q, *lo = (u64 *)(q + a8), *fst = (u64 *)(q + 2 * a8), *k_out = (u64 *)(q + 3 * a8),
+            *hi2 = (u64 *)(q + 4 * a8);
+        u32 *iota = (u32 *)(q + 5 * a8), *by_lo = (u32 *)(q + 5 * a8 + a4);
+        void *temp = q + 5 * a8 + 2 * a4;
+        wc::order_keys_kernel<<<e->num_sms * 2, 256, 0, e->stream>>>(
+            (const wc::WordRecord *)(dfin + off_w), n_w_max, e->d_cursors + kMaxParts, (const wc::LongRecord *)(dfin + off_x),
+            n_x_max, e->d_cursors + 2 * kMaxParts, (const u64 *)(dfin + off_b), hi, lo, fst, iota);
+        size_t tbx = tb;
+        CK(cub::DeviceRadixSort::SortPairs(temp, tbx, (const u64 *)lo, k_out, (const u32 *)iota, by_lo, n, 0, 64, e->stream));
+        wc::gather_u64_kernel<<<e->num_sms * 2, 256, 0, e->stream>>>(hi, by_lo, n_ord, hi2);
+        tbx = tb;
+        CK(cub::DeviceRadixSort::SortPairs(temp, tbx, (const u64 *)hi2, k_out, (const u32 *)by_lo, (u32 *)(dfin + off_pk), n, 0,
+                                           64, e->stream));
+        tbx = tb;
+        CK(cub::DeviceRadixSort::SortPairs(temp, tbx, (const u64 *)fst, k_out, (const u32 *)iota, (u32 *)(dfin + off_pf), n, 0,
+                                           64, e->stream));
+        CK(cudaGetLastError());
+        e->launches += 5;
+    }
+    // cursors into the head of the block: [0] word records, [1] long records, [2] blob bytes
+    CK(cudaMemcpyAsync(dfin, e->d_cursors + kMaxParts, sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
+    CK(cudaMemcpyAsync(dfin + 8, e->d_cursors + 2 * kMaxParts, 2 * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
+    CK(cudaMemcpyAsync(hfin, dfin, need, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    const double t_d2h = since();
+    const u64 n_w = ((const u64 *)hfin)[0], n_x = ((const u64 *)hfin)[1];
+    if (n_w > n_w_max || n_x > n_x_max) { e->err = "table entry counters are inconsistent"; return WC_ERR_CUDA; }
 
-    const u64 *w_keys = tab.data(), *w_counts = w_keys + 2 * s_n, *w_finv = w_keys + 3 * s_n;
-    const u64 *x_refs = tab.data() + 4 * s_n, *x_counts = x_refs + l_n, *x_finv = x_refs + 2 * l_n;
+    // Entries keep the record index space of the device order (word i -> i, long j -> n_w_max + j);
+    // slots without a record, and words whose count went back to zero, stay as count-0 entries.
+    const bool have_order = n_ord > 1;
     std::string blob;
     std::vector<wc::HostEntry> entries;
-    entries.reserve((size_t)(st.w_entries + st.x_entries));
-    for (size_t i = 0; i < s_n; i++) {
-        const u64 k[2] = {w_keys[2 * i], w_keys[2 * i + 1]};
-        if (k[0] == 0 || (int64_t)w_counts[i] == 0) continue;
-        const unsigned char *kb = (const unsigned char *)k; // the word itself, zero padded to 16
-        u32 len = 16;
-        while (len > 1 && kb[len - 1] == 0) len--;
-        entries.push_back(wc::HostEntry{blob.size(), len, (int64_t)w_counts[i], ~w_finv[i]});
-        blob.append((const char *)kb, len);
+    blob.reserve((size_t)n_w * 8 + blob_max);
+    const wc::WordRecord *wr = (const wc::WordRecord *)(hfin + off_w);
+    const wc::LongRecord *xr = (const wc::LongRecord *)(hfin + off_x);
+    if (have_order) entries.assign(n_ord, wc::HostEntry{0, 0, 0, ~0ull});
+    else entries.reserve((size_t)(n_w + n_x));
+    for (size_t i = 0; i < n_w; i++) {
+        const u64 k[2] = {wr[i].k0, wr[i].k1};
+        if ((int64_t)wr[i].count == 0) continue;
+        const u32 len = k[1] ? 16 - (u32)(__builtin_clzll(k[1]) >> 3) : 8 - (u32)(__builtin_clzll(k[0]) >> 3);
+        const wc::HostEntry he{blob.size(), len, (int64_t)wr[i].count, wr[i].first};
+        if (have_order) entries[i] = he; else entries.push_back(he);
+        blob.append((const char *)k, len); // the word itself (little-endian words: byte order is text order)
     }
     if (e->sort_mode) {
         u64 n_sorted = 0;
         rc = finish_sorted(e, st.stop, blob, entries, &n_sorted);
         if (rc != WC_OK) return rc;
     }
-    for (size_t i = 0; i < l_n; i++) {
-        const u64 r = x_refs[i];
-        if (r == 0 || (int64_t)x_counts[i] == 0) continue;
-        const u64 unit = r & ((1ull << 40) - 1);
-        const u64 len = arena[unit];
-        entries.push_back(wc::HostEntry{blob.size(), (u32)len, (int64_t)x_counts[i], ~x_finv[i]});
-        blob.append((const char *)&arena[unit + 1], (size_t)len);
+    for (size_t i = 0; i < n_x; i++) {
+        if ((int64_t)xr[i].count == 0) continue;
+        const wc::HostEntry he{blob.size(), (u32)xr[i].len, (int64_t)xr[i].count, xr[i].first};
+        if (have_order) entries[n_w_max + i] = he; else entries.push_back(he);
+        blob.append((const char *)(hfin + off_b + xr[i].blob_off), (size_t)xr[i].len);
     }
+    size_t n_distinct = 0;
+    for (const wc::HostEntry &he : entries) n_distinct += he.count != 0;
 
+    const double t_decode = since();
     wc_result *r = new (std::nothrow) wc_result();
     if (!r) return WC_ERR_NOMEM;
     const u64 total_bytes = e->job_stats_set ? e->job_bytes : e->consumed;
@@ -684,14 +773,19 @@ int wc_finish(wc_engine *e, wc_result **out) {
     r->stats.n_empty = st.n_empty;
     r->stats.n_lost_empty = lost;
     r->stats.stop = stop_abs - e->cfg.base_offset;
-    r->stats.n_distinct = entries.size();
+    r->stats.n_distinct = n_distinct;
     r->stats.n_long_words = st.n_long;
     r->stats.n_spilled = st.n_spill;
     r->stats.n_slow_tiles = st.n_slow_tiles;
     r->stats.table_grows = e->grows;
     r->stats.device_ms = e->device_ms;
     r->stats.count_kernel_ms = e->count_kernel_ms;
-    wc::finalize_rows(std::move(blob), entries, e->cfg.mode, st.n_empty, lost, r);
+    wc::finalize_rows(std::move(blob), entries, e->cfg.mode, st.n_empty, lost, r,
+                      have_order ? (const uint32_t *)(hfin + off_pk) : nullptr,
+                      have_order ? (const uint32_t *)(hfin + off_pf) : nullptr);
+    if (timing)
+        fprintf(stderr, "[wc] wc_finish: drain %.2f settle %.2f export+order+copy %.2f decode %.2f reduce %.2f ms\n", t_sync,
+                t_settle - t_sync, t_d2h - t_settle, t_decode - t_d2h, since() - t_decode);
     *out = r;
     return WC_OK;
 }
@@ -732,8 +826,6 @@ extern "C" uint32_t wc_debug_smem_slot(uint64_t key) {
 // Multi-GPU: shard counters and the key-owner exchange.  One engine per GPU counts
 // its byte range (wc_config.base_offset = where the range starts); the caller moves the exported
 // buffers between GPUs (NCCL all-to-all / gather through torch.distributed or any other transport).
-
-namespace { constexpr u32 kMaxParts = 64; }
 
 static int ensure_cursors(wc_engine *e) {
     if (!e->d_cursors) CK(cudaMalloc((void **)&e->d_cursors, (2 * kMaxParts + 2) * sizeof(u64)));

@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstring>
 #include <numeric>
+#include <chrono>
+#include <cstdlib>
 
 namespace wc {
 
@@ -16,7 +18,14 @@ namespace wc {
 // what it owns.  Empty words after the first non-empty one go to row 0 (main.cu:81-86 with the
 // all-zero slot of main.cu:154).
 void finalize_rows(std::string &&blob_in, std::vector<HostEntry> &v, int mode, uint64_t n_empty,
-                   uint64_t n_lost_empty, wc_result *out) {
+                   uint64_t n_lost_empty, wc_result *out, const uint32_t *by_key, const uint32_t *by_first) {
+    static const bool timing = getenv("WC_TIMING") != nullptr; // stderr: where the host reduce spends its time
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    const auto t_start = now();
+    auto t_keys = t_start, t_sort = t_start, t_sweep = t_start;
     out->blob = std::move(blob_in);
     out->rows.clear();
     out->total = 0;
@@ -24,40 +33,123 @@ void finalize_rows(std::string &&blob_in, std::vector<HostEntry> &v, int mode, u
     const size_t nd = v.size();
     if (nd == 0) return;
 
+    const bool pre_ordered = by_key != nullptr && by_first != nullptr;
+    std::vector<uint8_t> is_row;        // pre-ordered input: which entries become rows ...
+    std::vector<int64_t> row_count;     // ... and with what count
     if (mode == WC_MODE_EXACT) {
-        out->rows.reserve(nd);
-        for (const HostEntry &e : v) out->rows.push_back(Row{e.blob_off, e.len, e.count, e.first});
+        if (pre_ordered) {
+            is_row.assign(nd, 0); row_count.assign(nd, 0);
+            for (size_t i = 0; i < nd; i++) if (v[i].count != 0) { is_row[i] = 1; row_count[i] = v[i].count; }
+        } else {
+            out->rows.reserve(nd);
+            for (const HostEntry &e : v) out->rows.push_back(Row{e.blob_off, e.len, e.count, e.first});
+        }
     } else {
-        // bytewise order: every word is immediately followed by the words it is a prefix of
-        std::sort(v.begin(), v.end(), [blob](const HostEntry &a, const HostEntry &b) {
-            const uint32_t l = a.len < b.len ? a.len : b.len;
-            const int c = memcmp(blob + a.blob_off, blob + b.blob_off, l);
+        // `order`: entry indices in bytewise order of the words, so that every word is immediately
+        // followed by the words it is a prefix of.
+        std::vector<uint32_t> order;
+        order.reserve(nd);
+        auto tail_less = [blob, &v](uint32_t x, uint32_t y) { // words that agree on their first 16 bytes
+            const HostEntry &a = v[x], &b = v[y];
+            if (a.len <= 16 || b.len <= 16) return a.len < b.len;
+            const uint32_t l = (a.len < b.len ? a.len : b.len) - 16;
+            const int c = memcmp(blob + a.blob_off + 16, blob + b.blob_off + 16, l);
             if (c) return c < 0;
             return a.len < b.len;
-        });
-        std::vector<uint32_t> owner(nd), stk, best;
+        };
+        if (pre_ordered) {
+            for (size_t i = 0; i < nd; i++) if (by_key[i] < nd && v[by_key[i]].count != 0) order.push_back(by_key[i]);
+            // the device order looked at 16 bytes: put runs of longer words with equal heads right
+            for (size_t i = 0; i < order.size();) {
+                size_t j = i + 1;
+                if (v[order[i]].len >= 16)
+                    while (j < order.size() && v[order[j]].len >= 16 &&
+                           memcmp(blob + v[order[i]].blob_off, blob + v[order[j]].blob_off, 16) == 0) j++;
+                if (j - i > 1) std::sort(order.begin() + i, order.begin() + j, tail_less);
+                i = j;
+            }
+        } else {
+            // The sort runs on the first 16 bytes of each word as two big-endian integers (zero padded:
+            // a word holds no NUL byte, so padding sorts a prefix first); only words that agree on all
+            // 16 bytes fall back to comparing the rest.
+            struct SortKey { uint64_t hi, lo; uint32_t idx; };
+            std::vector<SortKey> keys;
+            keys.reserve(nd);
+            for (size_t i = 0; i < nd; i++) {
+                if (v[i].count == 0) continue;
+                unsigned char pad[16] = {0};
+                memcpy(pad, blob + v[i].blob_off, v[i].len < 16 ? v[i].len : 16);
+                uint64_t a, b;
+                memcpy(&a, pad, 8); memcpy(&b, pad + 8, 8);
+                keys.push_back(SortKey{__builtin_bswap64(a), __builtin_bswap64(b), (uint32_t)i});
+            }
+            t_keys = now();
+            std::sort(keys.begin(), keys.end(), [&tail_less](const SortKey &x, const SortKey &y) {
+                if (x.hi != y.hi) return x.hi < y.hi;
+                if (x.lo != y.lo) return x.lo < y.lo;
+                return tail_less(x.idx, y.idx);
+            });
+            for (const SortKey &k : keys) order.push_back(k.idx);
+        }
+        t_sort = now();
+        const size_t no = order.size();
+        // is word t a prefix of word w?  (t.len <= w.len checked by the caller)
+        auto is_prefix = [blob](const HostEntry &t, const HostEntry &w) {
+            return memcmp(blob + t.blob_off, blob + w.blob_off, t.len) == 0;
+        };
+        std::vector<uint32_t> owner(no), stk, best; // all three hold positions in `order`
         stk.reserve(64); best.reserve(64);
-        for (size_t i = 0; i <= nd; i++) {
+        for (size_t i = 0; i <= no; i++) {
             while (!stk.empty()) {
-                const HostEntry &t = v[stk.back()];
-                const bool open = i < nd && t.len <= v[i].len &&
-                                  memcmp(blob + t.blob_off, blob + v[i].blob_off, t.len) == 0;
+                const HostEntry &t = v[order[stk.back()]];
+                const bool open = i < no && t.len <= v[order[i]].len && is_prefix(t, v[order[i]]);
                 if (open) break;
                 owner[stk.back()] = best.back();
                 const uint32_t b = best.back();
                 stk.pop_back(); best.pop_back();
-                if (!best.empty() && v[b].first < v[best.back()].first) best.back() = b;
+                if (!best.empty() && v[order[b]].first < v[order[best.back()]].first) best.back() = b;
             }
-            if (i < nd) { stk.push_back((uint32_t)i); best.push_back((uint32_t)i); }
+            if (i < no) { stk.push_back((uint32_t)i); best.push_back((uint32_t)i); }
         }
-        std::vector<int64_t> acc(nd, 0);
-        for (size_t i = 0; i < nd; i++) acc[owner[i]] += v[i].count;
-        for (size_t i = 0; i < nd; i++)
-            if (owner[i] == i) out->rows.push_back(Row{v[i].blob_off, v[i].len, acc[i], v[i].first});
+        std::vector<int64_t> acc(no, 0);
+        for (size_t i = 0; i < no; i++) acc[owner[i]] += v[order[i]].count;
+        if (pre_ordered) {
+            is_row.assign(nd, 0); row_count.assign(nd, 0);
+            for (size_t i = 0; i < no; i++) if (owner[i] == i) { is_row[order[i]] = 1; row_count[order[i]] = acc[i]; }
+        } else {
+            for (size_t i = 0; i < no; i++)
+                if (owner[i] == i) {
+                    const HostEntry &e = v[order[i]];
+                    out->rows.push_back(Row{e.blob_off, e.len, acc[i], e.first});
+                }
+        }
     }
-    std::sort(out->rows.begin(), out->rows.end(), [](const Row &a, const Row &b) { return a.first < b.first; });
+    t_sweep = now();
+    if (pre_ordered) { // rows in order of first appearance: walk the device's order
+        size_t n_rows = 0;
+        for (uint8_t b : is_row) n_rows += b;
+        out->rows.reserve(n_rows);
+        for (size_t i = 0; i < nd; i++) {
+            const uint32_t x = by_first[i];
+            if (x < nd && is_row[x]) out->rows.push_back(Row{v[x].blob_off, v[x].len, row_count[x], v[x].first});
+        }
+    } else { // LSD radix sort on the 64-bit offset (11-bit digits, only the digits some offset uses)
+        std::vector<Row> &rows = out->rows, tmp(out->rows.size());
+        uint64_t all_or = 0;
+        for (const Row &r : rows) all_or |= r.first;
+        for (int shift = 0; shift < 64 && (all_or >> shift) != 0; shift += 11) {
+            size_t cnt[2049] = {0};
+            for (const Row &r : rows) cnt[((r.first >> shift) & 2047) + 1]++;
+            for (int d = 0; d < 2048; d++) cnt[d + 1] += cnt[d];
+            for (const Row &r : rows) tmp[cnt[(r.first >> shift) & 2047]++] = r;
+            rows.swap(tmp);
+        }
+    }
     if (mode != WC_MODE_EXACT && !out->rows.empty()) out->rows[0].count += (int64_t)(n_empty - n_lost_empty);
     for (const Row &r : out->rows) out->total += r.count;
+    if (timing)
+        fprintf(stderr, "[wc] finalize_rows: %zu words -> %zu rows; keys %.2f sort %.2f sweep %.2f order %.2f ms\n", nd,
+                out->rows.size(), ms(t_start, t_keys), ms(t_keys, t_sort), ms(t_sort, t_sweep), ms(t_sweep, now()));
 }
 
 } // namespace wc

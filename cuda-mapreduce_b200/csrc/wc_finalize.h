@@ -37,7 +37,11 @@ namespace wc {
 
 // Applies the reduce semantics of /root/reference/main.cu:57-108 in its order-free form
 // (SURVEY.md A.3).  `entries` index into `blob`; the result takes ownership of `blob`.
+// Optional, both or neither (wc_finish computes them on the GPU): `by_key` lists entry indices
+// ordered by the words' first 16 bytes (bytewise, shorter first; ties between longer words in any
+// order), `by_first` ordered by `first`; entries with count 0 are placeholders and are skipped.
 void finalize_rows(std::string &&blob, std::vector<HostEntry> &entries, int mode, uint64_t n_empty,
-                   uint64_t n_lost_empty, wc_result *out);
+                   uint64_t n_lost_empty, wc_result *out, const uint32_t *by_key = nullptr,
+                   const uint32_t *by_first = nullptr);
 
 } // namespace wc

@@ -94,6 +94,34 @@ __global__ void rehash_words_kernel(Tables T, const ulonglong2 *old_keys, const 
     }
 }
 
+// wc_finish: sort keys for the exported records, so that the host reduce starts from sorted lists.
+// Record index space: word record i -> i, long record j -> n_w_max + j.  hi/lo = the word's first 16
+// bytes as two big-endian integers (zero padded), fst = its first offset.  Slots past the number of
+// records actually written get all-ones keys (the host skips them by index).
+__device__ __forceinline__ u64 bswap64(u64 v) {
+    const u32 a = (u32)v, b = (u32)(v >> 32);
+    return ((u64)__byte_perm(a, 0, 0x0123) << 32) | (u64)__byte_perm(b, 0, 0x0123);
+}
+
+__global__ void order_keys_kernel(const WordRecord *w, u64 n_w_max, const u64 *n_w_ptr, const LongRecord *x, u64 n_x_max,
+                                  const u64 *n_x_ptr, const u64 *blob, u64 *hi, u64 *lo, u64 *fst, u32 *idx) {
+    const u64 n_w = *n_w_ptr, n_x = *n_x_ptr, n = n_w_max + n_x_max;
+    for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+        u64 h = ~0ull, l = ~0ull, f = ~0ull;
+        if (i < n_w_max) {
+            if (i < n_w) { h = bswap64(w[i].k0); l = bswap64(w[i].k1); f = w[i].first; }
+        } else if (i - n_w_max < n_x) {
+            const LongRecord r = x[i - n_w_max];
+            h = bswap64(blob[r.blob_off >> 3]); l = bswap64(blob[(r.blob_off >> 3) + 1]); f = r.first;
+        }
+        hi[i] = h; lo[i] = l; fst[i] = f; idx[i] = (u32)i;
+    }
+}
+
+__global__ void gather_u64_kernel(const u64 *src, const u32 *idx, u64 n, u64 *dst) {
+    for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) dst[i] = src[idx[i]];
+}
+
 __global__ void count_long_kernel(Tables T, u64 *out) { // out[0] entries, out[1] blob bytes (padded to 8 each)
     const u64 n = 1ull << T.x_log2;
     for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {

@@ -150,9 +150,9 @@ class Result:
         st = Stats()
         L.wc_result_stats(handle, C.byref(st))
         self.stats = {k: getattr(st, k) for k, _ in Stats._fields_}
-        need = L.wc_result_render(handle, None, 0)
         self.rows, self.firsts = [], []
         if keep_rows:
+            need = L.wc_result_render(handle, None, 0)
             buf = C.create_string_buffer(need)
             L.wc_result_render(handle, buf, need)
             self.rendered = buf.raw[:need]
