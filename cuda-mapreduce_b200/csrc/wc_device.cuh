@@ -637,7 +637,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
     const Tables &T = *Tp;
     const u64 delta = Lp->negate ? ~0ull : 1ull;
     constexpr int R = kDrainBatch / 32;
-    u32 n_wnew = 0, n_xnew = 0, n_spill = 0;
+    u32 n_wnew = 0, n_xnew = 0, n_spill = 0, n_long = 0;
 #ifdef WC_PROFILE
     long long pc_wait = 0, pc_claim = 0, pc_glob = 0, pc_batches = 0, pc_t = clock64();
 #endif
@@ -696,6 +696,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
             rec[j].w &= 0x7FFFu;                 // the word's length, saturated ...
             if (rec[j].w > 16) rec[j].w = rec[j].x; // ... a 17+ byte word carries its full length instead of its first bytes
             const u32 len = rec[j].w;
+            n_long += len > 8;
             if (len <= 8 && slot_taken) { todo |= 1u << j; n_spill++; }
             else if (len <= 8) { // the slot looked free: claim it (this is how the CTA's table fills up)
                 const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
@@ -756,7 +757,9 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
     n_wnew = __reduce_add_sync(0xFFFFFFFFu, n_wnew);
     n_xnew = __reduce_add_sync(0xFFFFFFFFu, n_xnew);
     n_spill = __reduce_add_sync(0xFFFFFFFFu, n_spill);
+    n_long = __reduce_add_sync(0xFFFFFFFFu, n_long);
     if (lane == 0) {
+        if (n_long && !Lp->negate) red_add_u64(&T.st->n_long, (u64)n_long);
         if (n_wnew) red_add_u64(&T.st->w_entries, (u64)n_wnew);
         if (n_xnew) red_add_u64(&T.st->x_entries, (u64)n_xnew);
         if (n_spill && !Lp->negate) red_add_u64(&T.st->n_spill, (u64)n_spill);
@@ -789,14 +792,9 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     __shared__ u32 s_first_ws;
     __shared__ u64 s_stop;
     __shared__ DefCtl s_ctl;
-    __shared__ uint2 s_keep[17]; // s_keep[n]: mask that keeps the first n bytes of an 8-byte key (n >= 8: all)
 
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     Status *st = T.st;
-    if (tid < 17) {
-        const u64 m = tid >= 8 ? ~0ull : ((1ull << (8 * tid)) - 1);
-        s_keep[tid] = make_uint2((u32)m, (u32)(m >> 32));
-    }
 
     // ---- which part of the piece does this launch cover?  (One thread reads STOP so that the
     // whole CTA takes the same branch even while other CTAs are still lowering it.)
@@ -863,7 +861,6 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     }
     const u32 lt_mask = (1u << lane) - 1;
 
-    u32 n_long = 0;                                  // per lane: words of 9+ bytes
     u32 acc_flush = 0, acc_empty = 0, acc_slow = 0;  // per lane; a warp's range is < 4 GiB
     bool seen_nonempty = L.negate != 0;              // roll-back launches do not look for P0
     u32 p0_rel = 0, my_empties_before = 0;           // P0 relative to cta_base
@@ -1026,10 +1023,8 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
 #endif
                     const u32 k = k0 + lane;
                     const u32 d = k < total ? (u32)dl[k] : 0u;
-                    const u32 d_up = __shfl_up_sync(0xFFFFFFFFu, d, 1);
-                    const int before = k0 ? (int)(dl[k0 - 1] & 0x3FFu) : first_prev; // same for every lane
                     const int e = (int)(d & 0x3FFu);
-                    const int prev = lane ? (int)(d_up & 0x3FFu) : before;
+                    const int prev = k ? (int)(dl[k - 1] & 0x3FFu) : first_prev; // the delimiter before this one
                     const int len = e - prev - 1;
                     const bool word = (d >> 15) && len > 0;       // a flush of a non-empty word
                     const int rlen = len > 16 ? 16 : (len < 1 ? 1 : len); // bytes looked at (keeps reads in bounds)
@@ -1038,9 +1033,9 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const u32 idx = (u32)(16 + e - rlen);          // >= 0: reaches into the previous tile's tail
                     const u32 *r = ring32 + (idx >> 2);
                     const u32 w0 = r[0], w1 = r[1], w2 = r[2];
-                    const uint2 keep = s_keep[rlen];
+                    const u64 keep = ~0ull >> (8u * (8u - (u32)(rlen > 8 ? 8 : rlen))); // the first min(len, 8) bytes
                     const u32 sh = (idx & 3) * 8;
-                    const u32 klo = __funnelshift_r(w0, w1, sh) & keep.x, khi = __funnelshift_r(w1, w2, sh) & keep.y;
+                    const u32 klo = __funnelshift_r(w0, w1, sh) & (u32)keep, khi = __funnelshift_r(w1, w2, sh) & (u32)(keep >> 32);
 
                     if (L.em.cursor != nullptr) { // ---- sort path: write the word out instead of counting it
                         const bool emit = word && len <= 16 && !L.negate; // (what lies after STOP is dropped at the end)
@@ -1052,9 +1047,9 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                             if (emit && at < L.em.cap) {
                                 u32 k1lo = 0, k1hi = 0;
                                 if (len > 8) { // bytes 8..15
-                                    const uint2 keep1 = s_keep[len - 8];
-                                    k1lo = __funnelshift_r(w2, r[3], sh) & keep1.x;
-                                    k1hi = __funnelshift_r(r[3], r[4], sh) & keep1.y;
+                                    const u64 keep1 = ~0ull >> (8u * (16u - (u32)len));
+                                    k1lo = __funnelshift_r(w2, r[3], sh) & (u32)keep1;
+                                    k1hi = __funnelshift_r(r[3], r[4], sh) & (u32)(keep1 >> 32);
                                 }
                                 const u64 k0 = (u64)klo | ((u64)khi << 32), k1 = (u64)k1lo | ((u64)k1hi << 32);
                                 L.em.key[at] = make_ulonglong2(k0, k1); // (sort keys are derived from these at the end)
@@ -1074,7 +1069,6 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                                 __nanosleep(64);
                             }
                             if (dlong) def_ring[cell] = make_uint4((u32)len, khi, relT + (u32)e, ring_full_word(pos, (u32)len, false));
-                            n_long += dlong;
                         }
                         continue;
                     }
@@ -1104,7 +1098,6 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                                 make_uint4(len > 16 ? (u32)len : klo, khi, rel,
                                            ((u32)len > 0x7FFFu ? 0x7FFFu : (u32)len) | ((ent.x | ent.y) != 0 ? 0x8000u : 0u));
                         n_staged += __popc(bq);
-                        n_long += defer && len > 8;
                         if (n_staged > kStageCap - 32) { // the next round might not fit
                             __syncwarp();
                             flush_stage(stage, n_staged, def_ring, &s_ctl, st);
@@ -1121,12 +1114,10 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     }
     // ---- per-warp results
     const u64 w_flush = warp_sum64(acc_flush), w_empty = warp_sum64(acc_empty);
-    const u32 w_long = __reduce_add_sync(0xFFFFFFFFu, n_long);
     if (lane == 0) {
         if (w_flush) atomicAdd(&st->n_flush, L.negate ? (u64)(-(long long)w_flush) : w_flush);
         if (w_empty) atomicAdd(&st->n_empty, L.negate ? (u64)(-(long long)w_empty) : w_empty);
         if (!L.negate) {
-            if (w_long) atomicAdd(&st->n_long, (u64)w_long);
             if (acc_slow) atomicAdd(&st->n_slow_tiles, (u64)acc_slow);
             if (L.ws != nullptr && gwarp < L.n_ws) {
                 L.ws[gwarp].p0 = (seen_nonempty && t0 < t1) ? L.base + cta_base + p0_rel : kNone;
