@@ -767,6 +767,16 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
 }
 
 
+// a16 / b16: this lane's 16-bit masks of bytes [16*lane, +16) of a tile's first and second 512 bytes.
+// Returns the 32-bit mask of bytes [32*lane, +32) of the tile.
+__device__ __forceinline__ u32 halves_to_lanes(u32 a16, u32 b16) {
+    const u32 lane = lane_id();
+    const u32 both = (a16 & 0xFFFFu) | (b16 << 16);
+    const u32 x0 = __shfl_sync(0xFFFFFFFFu, both, (2 * lane) & 31), x1 = __shfl_sync(0xFFFFFFFFu, both, (2 * lane + 1) & 31);
+    const u32 sh = lane < 16 ? 0u : 16u;
+    return ((x0 >> sh) & 0xFFFFu) | (((x1 >> sh) & 0xFFFFu) << 16);
+}
+
 // One lane's two 16-byte pieces of tile `tile` into its buffer: asynchronous copies when the
 // bytes are all inside the input, a padded synchronous load at the very end of it.
 __device__ __forceinline__ void fetch_tile(const Launch &L, u64 tile, unsigned char *buf, u32 lane) {
@@ -880,6 +890,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                 *reinterpret_cast<uint4 *>(wbase + (t0 & 1) * kBufBytes) = load16(L.buf, L.n, (u64)t0 * kTile - 16);
         }
         fetch_tile(L, t0, wbase + (t0 & 1) * kBufBytes, lane);
+        const u32 last_tile = (u32)((L.n - 1) / kTile); // holds the piece's last byte
         for (u32 t = t0; t < t1; ++t) {
             unsigned char *buf = wbase + (t & 1) * kBufBytes;
             asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -890,129 +901,116 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                 fetch_tile(L, t + 1, nbuf, lane);
             }
             const u32 *ring32 = reinterpret_cast<const u32 *>(buf);
-            const uint4 va = *reinterpret_cast<const uint4 *>(buf + 16 + lane * 16);
-            const uint4 vb = *reinterpret_cast<const uint4 *>(buf + 16 + kSub + lane * 16);
+            // Each lane owns 32 consecutive bytes of the tile: one 32-bit mask per property.
+            const uint4 va = *reinterpret_cast<const uint4 *>(buf + 16 + lane * 32);
+            const uint4 vb = *reinterpret_cast<const uint4 *>(buf + 32 + lane * 32);
             const u64 T0 = (u64)t * kTile;          // buffer-relative offset of this tile
             const u32 relT = (u32)(T0 - cta_base);
 
             // ---- classify 2 x 16 bytes
-            u32 dmA, dmB, lfA, lfB, liveA, liveB;
+            u32 dm, lf, live;
             {
-                // (one sub-tile at a time: keeps the number of live registers down)
+                // (one half at a time: keeps the number of live registers down)
                 u32 ex;
                 {
                     const FastFlags a0 = classify_fast4(va.x), a1 = classify_fast4(va.y), a2 = classify_fast4(va.z),
                                     a3 = classify_fast4(va.w);
-                    dmA = movemask16(a0.cand, a1.cand, a2.cand, a3.cand);
-                    lfA = movemask16(a0.lf, a1.lf, a2.lf, a3.lf);
+                    dm = movemask16(a0.cand, a1.cand, a2.cand, a3.cand);
+                    lf = movemask16(a0.lf, a1.lf, a2.lf, a3.lf);
                     ex = a0.ex | a1.ex | a2.ex | a3.ex;
                 }
                 asm volatile("" ::: "memory");
                 {
                     const FastFlags b0 = classify_fast4(vb.x), b1 = classify_fast4(vb.y), b2 = classify_fast4(vb.z),
                                     b3 = classify_fast4(vb.w);
-                    dmB = movemask16(b0.cand, b1.cand, b2.cand, b3.cand);
-                    lfB = movemask16(b0.lf, b1.lf, b2.lf, b3.lf);
+                    dm |= movemask16(b0.cand, b1.cand, b2.cand, b3.cand) << 16;
+                    lf |= movemask16(b0.lf, b1.lf, b2.lf, b3.lf) << 16;
                     ex |= b0.ex | b1.ex | b2.ex | b3.ex;
                 }
-                liveA = dmA; liveB = dmB;
+                live = dm;
                 if (__any_sync(0xFFFFFFFFu, ex != 0) || killed) {
+                    // The exact path sees the tile as two 512-byte halves of 16 bytes per lane; its masks
+                    // are handed back to the lanes that own those bytes here.
                     acc_slow += lane == 0;
-                    const ExactOut oa = exact_sub(va, killed, L.buf, L.n, L.base, T0, &st->stop, L.negate);
-                    const ExactOut ob = exact_sub(vb, oa.killed_out, L.buf, L.n, L.base, T0 + kSub, &st->stop, L.negate);
-                    dmA = oa.dm; liveA = oa.live; lfA = oa.lfm;
-                    dmB = ob.dm; liveB = ob.live; lfB = ob.lfm;
+                    const uint4 xa = *reinterpret_cast<const uint4 *>(buf + 16 + lane * 16);
+                    const uint4 xb = *reinterpret_cast<const uint4 *>(buf + 16 + kSub + lane * 16);
+                    const ExactOut oa = exact_sub(xa, killed, L.buf, L.n, L.base, T0, &st->stop, L.negate);
+                    const ExactOut ob = exact_sub(xb, oa.killed_out, L.buf, L.n, L.base, T0 + kSub, &st->stop, L.negate);
+                    dm = halves_to_lanes(oa.dm, ob.dm); live = halves_to_lanes(oa.live, ob.live);
+                    lf = halves_to_lanes(oa.lfm, ob.lfm);
                     killed = ob.killed_out != 0;
                 }
             }
 
-            // ---- what the byte before each lane's 16 bytes was: bit 0 line feed, bit 1 delimiter
-            u32 prevA, prevB;
+            // ---- what the byte before this lane's 32 bytes was: bit 0 line feed, bit 1 delimiter
+            u32 prev;
             {
-                const u32 mineA = (lfA >> 15) | ((dmA >> 15) << 1), mineB = (lfB >> 15) | ((dmB >> 15) << 1);
-                const u32 upA = __shfl_up_sync(0xFFFFFFFFu, mineA, 1), upB = __shfl_up_sync(0xFFFFFFFFu, mineB, 1);
-                const u32 lastA = __shfl_sync(0xFFFFFFFFu, mineA, 31);
-                prevA = lane == 0 ? ((last_is_lf ? 1u : 0u) | (carry_prev == -1 ? 2u : 0u)) : upA;
-                prevB = lane == 0 ? lastA : upB;
-                last_is_lf = (__shfl_sync(0xFFFFFFFFu, mineB, 31) & 1u) != 0;
+                const u32 mine = (lf >> 31) | ((dm >> 31) << 1);
+                const u32 up = __shfl_up_sync(0xFFFFFFFFu, mine, 1);
+                prev = lane == 0 ? ((last_is_lf ? 1u : 0u) | (carry_prev == -1 ? 2u : 0u)) : up;
+                last_is_lf = (__shfl_sync(0xFFFFFFFFu, mine, 31) & 1u) != 0;
             }
             // ---- STOP: a line that is just "\n" (main.cu:185), or a 1-byte tail at the very end
             if (!L.negate) {
-                const u32 startA = ((lfA << 1) | (prevA & 1u)) & 0xFFFFu, startB = ((lfB << 1) | (prevB & 1u)) & 0xFFFFu;
-                const u32 blankA = lfA & startA, blankB = lfB & startB; // bit p: byte p starts a line
-                if (blankA) atomicMin(&st->stop, L.base + T0 + lane * 16 + (__ffs(blankA) - 1));
-                if (blankB) atomicMin(&st->stop, L.base + T0 + kSub + lane * 16 + (__ffs(blankB) - 1));
-                if (L.last_piece && L.n - 1 >= T0 && L.n - 1 < T0 + kTile) {
+                const u32 start = (lf << 1) | (prev & 1u); // bit p: byte p starts a line
+                const u32 blank = lf & start;
+                if (blank) atomicMin(&st->stop, L.base + T0 + lane * 32 + (__ffs(blank) - 1));
+                if (t == last_tile && L.last_piece) {
                     const u32 q = (u32)(L.n - 1 - T0); // position of the last byte in this tile
-                    const u32 own = q & 511, p = own & 15;
-                    const u32 starts = q < kSub ? startA : startB;
-                    if ((own >> 4) == lane && ((starts >> p) & 1)) atomicMin(&st->stop, L.base + L.n - 1);
+                    if ((q >> 5) == lane && ((start >> (q & 31)) & 1)) atomicMin(&st->stop, L.base + L.n - 1);
                 }
             }
 
             // Roll-back launches only see flush points at or after range_lo.
             if (range_lo > T0) {
-                const u64 loA = T0 + lane * 16, loB = loA + kSub;
-                if (range_lo >= loA + 16) liveA = 0;
-                else if (range_lo > loA) liveA &= ~((1u << (u32)(range_lo - loA)) - 1);
-                if (range_lo >= loB + 16) liveB = 0;
-                else if (range_lo > loB) liveB &= ~((1u << (u32)(range_lo - loB)) - 1);
+                const u64 lo = T0 + lane * 32;
+                if (range_lo >= lo + 32) live = 0;
+                else if (range_lo > lo) live &= ~((1u << (u32)(range_lo - lo)) - 1);
             }
 
             // ---- flush counts straight from the masks: a flush right after a delimiter is an empty word
-            const u32 afterA = ((dmA << 1) | (prevA >> 1)) & 0xFFFFu, afterB = ((dmB << 1) | (prevB >> 1)) & 0xFFFFu;
-            const u32 emA = liveA & afterA, emB = liveB & afterB;
-            acc_flush += __popc(liveA) + __popc(liveB);
-            acc_empty += __popc(emA) + __popc(emB);
+            const u32 after = (dm << 1) | (prev >> 1);
+            const u32 em = live & after;
+            acc_flush += __popc(live);
+            acc_empty += __popc(em);
             if (!seen_nonempty) { // this warp's first non-empty word, and the empty ones before it
-#pragma unroll
-                for (int sub = 0; sub < 2 && !seen_nonempty; sub++) {
-                    const u32 ne = sub ? (liveB & ~afterB) : (liveA & ~afterA), em = sub ? emB : emA;
-                    const u32 bn = __ballot_sync(0xFFFFFFFFu, ne != 0);
-                    u32 x = __popc(em);
-                    if (bn) {
-                        const u32 fl = __ffs(bn) - 1;
-                        const u32 pf = __shfl_sync(0xFFFFFFFFu, ne ? __ffs(ne) - 1 : 0, fl);
-                        if (lane == fl) x = __popc(em & ((1u << pf) - 1));
-                        if (lane > fl) x = 0;
-                        p0_rel = relT + sub * kSub + fl * 16 + pf;
-                        seen_nonempty = true;
-                    }
-                    my_empties_before += __reduce_add_sync(0xFFFFFFFFu, x);
+                const u32 ne = live & ~after;
+                const u32 bn = __ballot_sync(0xFFFFFFFFu, ne != 0);
+                u32 x = __popc(em);
+                if (bn) {
+                    const u32 fl = __ffs(bn) - 1;
+                    const u32 pf = __shfl_sync(0xFFFFFFFFu, ne ? __ffs(ne) - 1 : 0, fl);
+                    if (lane == fl) x = __popc(em & ((1u << pf) - 1));
+                    if (lane > fl) x = 0;
+                    p0_rel = relT + fl * 32 + pf;
+                    seen_nonempty = true;
                 }
+                my_empties_before += __reduce_add_sync(0xFFFFFFFFu, x);
             }
 
-            // ---- position-ordered list of every delimiter; one scan serves both sub-tiles
-            const u32 cntA = __popc(dmA), cntB = __popc(dmB);
-            const u32 incl = warp_incl_scan(cntA | (cntB << 16));
+            // ---- position-ordered list of every delimiter
+            const u32 cnt = __popc(dm);
+            const u32 incl = warp_incl_scan(cnt);
             const u32 tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
-            const u32 totA = tot & 0xFFFFu, totB = tot >> 16;
-            const u32 exclA = (incl & 0xFFFFu) - cntA, exclB = (incl >> 16) - cntB;
+            const u32 excl = incl - cnt;
 
-            // The list holds at most kDlCap entries: a tile dense with delimiters is done one sub-tile
-            // at a time.  `first_prev` is the position (tile relative, negative if it lies before the
-            // tile) of the delimiter that precedes list entry 0.
+            // The list holds at most kDlCap entries: a tile dense with delimiters is done one half (16
+            // lanes) at a time.  `first_prev` is the position (tile relative, negative if it lies before
+            // the tile) of the delimiter that precedes list entry 0.
             int first_prev = carry_prev;
-            const bool dense = totA + totB > (u32)kDlCap;
+            const bool dense = tot > (u32)kDlCap;
+            const u32 half0 = __shfl_sync(0xFFFFFFFFu, excl, 16); // delimiters in the first 512 bytes
             for (int ph = 0; ph < (dense ? 2 : 1); ph++) {
-                if (!dense || ph == 0) {
-                    u32 m = dmA;
-                    unsigned short *o = dl + exclA;
+                if (!dense || (ph == 0) == (lane < 16)) {
+                    u32 m = dm;
+                    unsigned short *o = dl + excl - ((dense && ph) ? half0 : 0u);
                     while (m) {
                         const u32 p = __ffs(m) - 1; m &= m - 1;
-                        *o++ = (unsigned short)((lane * 16 + p) | (((liveA >> p) & 1u) << 15));
-                    }
-                }
-                if (!dense || ph == 1) {
-                    u32 m = dmB;
-                    unsigned short *o = dl + (dense ? 0u : totA) + exclB;
-                    while (m) {
-                        const u32 p = __ffs(m) - 1; m &= m - 1;
-                        *o++ = (unsigned short)((kSub + lane * 16 + p) | (((liveB >> p) & 1u) << 15));
+                        *o++ = (unsigned short)((lane * 32 + p) | (((live >> p) & 1u) << 15));
                     }
                 }
                 __syncwarp();
-                const u32 total = dense ? (ph ? totB : totA) : totA + totB;
+                const u32 total = dense ? (ph ? tot - half0 : half0) : tot;
 
                 // ---- one word per lane: a hit in the CTA's table is counted here, everything else
                 // (misses, words of 9+ bytes) is queued for drain_deferred()
