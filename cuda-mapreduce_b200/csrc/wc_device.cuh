@@ -185,6 +185,23 @@ __device__ __forceinline__ u64 load8_unaligned(const uint8_t *buf, u64 off, u32 
     return v;
 }
 
+// The same in two steps, so that several reads can be in flight before the first is used.
+struct Raw8 { u64 a, b; u32 o, nbytes; };
+__device__ __forceinline__ Raw8 load8_issue(const uint8_t *buf, u64 off, u32 nbytes) {
+    const u64 *p = reinterpret_cast<const u64 *>(buf + (off & ~7ull));
+    Raw8 r;
+    r.o = (u32)(off & 7); r.nbytes = nbytes;
+    r.a = __ldg(p);
+    r.b = (r.o + nbytes > 8) ? __ldg(p + 1) : 0ull;
+    return r;
+}
+__device__ __forceinline__ u64 load8_finish(const Raw8 &r) {
+    u64 v = r.a >> (r.o * 8);
+    if (r.o) v |= r.b << (64 - r.o * 8);
+    if (r.nbytes < 8) v &= (1ull << (8 * r.nbytes)) - 1;
+    return v;
+}
+
 __device__ __forceinline__ u64 warp_sum64(u64 v) {
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
@@ -277,7 +294,10 @@ struct Bucket { ulonglong2 k[kBucket]; };
 // Home bucket (its first slot) of a word of 1..16 bytes: a function of its first 8 bytes and its
 // length only, so that it is known before bytes 8..15 have been fetched.
 __device__ __forceinline__ u32 word_home(const Tables &T, u64 k0, u32 len) {
-    return (hash_key128((u32)k0, (u32)(k0 >> 32), len, 0x5bd1e995u) >> (32 + kBucketLog2 - T.w_log2)) * kBucket;
+    u32 h = (u32)k0 * 0x9E3779B1u + (u32)(k0 >> 32) * 0x85EBCA77u + len * 0xC2B2AE3Du;
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du; // (the high bits pick the bucket)
+    return (h >> (32 + kBucketLog2 - T.w_log2)) * kBucket;
 }
 
 __device__ __forceinline__ Bucket load_bucket(const Tables &T, u32 slot) {
@@ -687,46 +707,51 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
 #ifdef WC_PROFILE
         { long long t = clock64(); pc_wait += t - pc_t; pc_t = t; pc_batches++; }
 #endif
-        u32 slot[R]; Bucket key[R]; u64 k1[R];
+        // Decode, then issue every global read of the batch (the home bucket of each 1..16 byte word
+        // and bytes 8..15 of the longer ones) BEFORE touching the shared-memory table: the claims below
+        // run while those reads are in flight.  A word whose claim succeeds wasted one read.
+        u32 slot[R]; Bucket key[R]; Raw8 raw[R];
         u32 todo = 0; // bit j: record j goes to the global word table
 #pragma unroll
         for (int j = 0; j < R; j++) {
+            slot[j] = 0; raw[j] = Raw8{0, 0, 0, 8};
             if (!(live & (1u << j))) { rec[j] = make_uint4(0, 0, 0, 0); continue; }
             const bool slot_taken = (rec[j].w & 0x8000u) != 0;
             rec[j].w &= 0x7FFFu;                 // the word's length, saturated ...
             if (rec[j].w > 16) rec[j].w = rec[j].x; // ... a 17+ byte word carries its full length instead of its first bytes
             const u32 len = rec[j].w;
             n_long += len > 8;
-            if (len <= 8 && slot_taken) { todo |= 1u << j; n_spill++; }
-            else if (len <= 8) { // the slot looked free: claim it (this is how the CTA's table fills up)
+            if (len <= 16) {
                 const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-                const u32 sidx = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
-                const u64 old = atoms_cas_u64(&tab[sidx], 0ull, k0);
-                if (old == 0 || old == k0) {
-                    u32 *cell = reinterpret_cast<u32 *>(&tab[sidx]);
-                    reds_add_u32(cell + 2, (u32)delta);
-                    reds_min_u32(cell + 3, rec[j].z);
-                } else { todo |= 1u << j; n_spill++; }
-            } else if (len <= 16) todo |= 1u << j;
+                slot[j] = word_home(T, k0, len);
+                key[j] = load_bucket(T, slot[j]);
+                if (len > 8) raw[j] = load8_issue(Lp->buf, cta_base + rec[j].z - len + 8, len - 8);
+                if (len > 8 || slot_taken) todo |= 1u << j;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < R; j++) { // the slot looked free: claim it (this is how the CTA's table fills up)
+            const u32 len = rec[j].w;
+            if (len == 0 || len > 8) continue;
+            if (todo & (1u << j)) { n_spill++; continue; }
+            const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
+            const u32 sidx = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
+            const u64 old = atoms_cas_u64(&tab[sidx], 0ull, k0);
+            if (old == 0 || old == k0) {
+                u32 *cell = reinterpret_cast<u32 *>(&tab[sidx]);
+                reds_add_u32(cell + 2, (u32)delta);
+                reds_min_u32(cell + 3, rec[j].z);
+            } else { todo |= 1u << j; n_spill++; }
         }
 #ifdef WC_PROFILE
         { long long t = clock64(); pc_claim += t - pc_t; pc_t = t; }
 #endif
 #pragma unroll
-        for (int j = 0; j < R; j++) { // issue every global read of the batch ...
-            const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-            slot[j] = 0; k1[j] = 0;
-            if (todo & (1u << j)) {
-                slot[j] = word_home(T, k0, rec[j].w);
-                key[j] = load_bucket(T, slot[j]);
-                if (rec[j].w > 8) k1[j] = load8_unaligned(Lp->buf, cta_base + rec[j].z - rec[j].w + 8, rec[j].w - 8);
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < R; j++) { // ... before the first one is used
+        for (int j = 0; j < R; j++) {
             const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
             const u64 end = cta_base + rec[j].z; // buffer-relative offset of the delimiter
-            if (todo & (1u << j)) n_wnew += word_insert_at(T, k0, k1[j], delta, Lp->base + end, slot[j], key[j]);
+            if (todo & (1u << j))
+                n_wnew += word_insert_at(T, k0, rec[j].w > 8 ? load8_finish(raw[j]) : 0ull, delta, Lp->base + end, slot[j], key[j]);
         }
         // 17+ byte words last and on their own: a function call between the loads above and their use
         // would push every loaded key through the stack.
