@@ -21,6 +21,7 @@ this size is the capacity-lifted restatement in oracle/.
 """
 import argparse
 import json
+import re
 import os
 import subprocess
 import sys
@@ -145,6 +146,19 @@ def run_reference(args):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def ncu_traffic(workload, nbytes):
+    """dram__bytes_read + dram__bytes_write of one forward count_kernel launch, from the newest ncu
+    --set full capture committed under profiles/ (tools/ncu_summary.py); only for the workload and
+    size that capture was taken on."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")),
+                   key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])
+    if not files or workload != "config2" or nbytes != 1_000_000_000:
+        return None, None
+    d = json.load(open(files[-1]))
+    return d["traffic_bytes_per_launch"], "profiles/" + os.path.basename(files[-1])
 
 
 def main():
@@ -288,12 +302,13 @@ def main():
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_val = all_bytes / te.item() / 1e9
-    d2h = 8 * (4 * (1 << wp["s_log2"]) + 3 * (1 << wp["l_log2"])) + 512
+    e2e_val = all_bytes / te.item() / 1e9 if e2e_steps else None
+    d2h = eng.finish_d2h_bytes()  # what the last wc_finish copied: counters, used entries, their two orders
 
     if rank != 0:
         return
     peak, peak_src = measured_peak()
+    traffic, traffic_src = ncu_traffic(args.workload, nbytes)
     achieved = nbytes / (kernel_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -309,10 +324,10 @@ def main():
         "words_per_s": all_words / (ms_step * 1e-3),
         "frac_of_hbm_nominal_8TBs": value / world / 8000.0,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "wc::count_kernel (forward launch)",
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": "wc::count_kernel (forward launch)",
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": nbytes},
-        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": d2h,
-                "ms_per_step": te.item() * 1e3},
+        "e2e": ({"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": d2h,
+                 "ms_per_step": te.item() * 1e3} if e2e_steps else None),
         "gpu_launches": int(launches) * args.steps,
         "clocks": clocks,
     }

@@ -59,6 +59,7 @@ struct wc_engine {
     u64 *d_cursors = nullptr;   // shuffle: per-partition counts / cursors (2 * kMaxParts + 2 words)
     void *d_fin = nullptr, *h_fin = nullptr; // wc_finish: the used table entries, compacted (device / pinned host)
     size_t d_fin_cap = 0, h_fin_cap = 0;
+    u64 finish_d2h = 0;                      // bytes the last wc_finish brought to the host
     void *d_ord = nullptr;                   // wc_finish: sort keys and cub scratch
     size_t d_ord_cap = 0;
     bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
@@ -604,6 +605,8 @@ int wc_device_ms(wc_engine *e, double *ms, double *count_kernel_ms, uint64_t *ke
     return WC_OK;
 }
 
+uint64_t wc_finish_d2h_bytes(const wc_engine *e) { return e ? e->finish_d2h : 0; }
+
 void *wc_stream(wc_engine *e) { return e ? (void *)e->stream : nullptr; }
 
 int wc_host_alloc(void **p, size_t n) {
@@ -725,6 +728,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
     CK(cudaMemcpyAsync(dfin + 8, e->d_cursors + 2 * kMaxParts, 2 * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
     CK(cudaMemcpyAsync(hfin, dfin, need, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    e->finish_d2h = need + sizeof(wc::Status);
     const double t_d2h = since();
     const u64 n_w = ((const u64 *)hfin)[0], n_x = ((const u64 *)hfin)[1];
     if (n_w > n_w_max || n_x > n_x_max) { e->err = "table entry counters are inconsistent"; return WC_ERR_CUDA; }

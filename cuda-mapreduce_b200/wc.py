@@ -103,6 +103,8 @@ def lib():
     L.wc_host_alloc.argtypes = [C.POINTER(vp), sz]
     L.wc_host_free.argtypes = [vp]
     L.wc_device_ms.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(u64)]
+    L.wc_finish_d2h_bytes.argtypes = [vp]
+    L.wc_finish_d2h_bytes.restype = u64
     L.wc_stream.argtypes = [vp]
     L.wc_stream.restype = vp
     L.wc_debug_finalize.argtypes = [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(i64), C.POINTER(u64), sz, C.c_int,
@@ -252,6 +254,9 @@ class Engine:
 
     def import_long(self, dev_meta, n, dev_blob):
         self._ck(lib().wc_import_long(self.h, C.c_void_p(dev_meta), n, C.c_void_p(dev_blob)))
+
+    def finish_d2h_bytes(self):
+        return lib().wc_finish_d2h_bytes(self.h)
 
     def device_ms(self):
         ms, kms, n = C.c_double(), C.c_double(), C.c_uint64()

@@ -148,6 +148,11 @@ WC_API int wc_host_free(void *p);
  * kernels were launched. */
 WC_API int wc_device_ms(wc_engine *e, double *ms, double *count_kernel_ms, uint64_t *kernel_launches);
 
+/* Bytes the last wc_finish() copied from the device to the host (counters + the used table entries
+ * and their two sort orders; the tables themselves stay on the device).  No reference counterpart:
+ * main.cu:158 copies its ten output rows unconditionally. */
+WC_API uint64_t wc_finish_d2h_bytes(const wc_engine *e);
+
 /* The CUDA stream (cudaStream_t) the engine launches on, for callers that
  * bracket work with their own events. */
 WC_API void *wc_stream(wc_engine *e);

@@ -1,4 +1,3 @@
-timeout 200 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-python bench.py --no-cpu-baseline --no-e2e --steps 10 --warmup 3 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('default', d['value'], d['ms_per_step'])"
-for v in $VARIANTS; do WC_LIB=$PWD/cuda-mapreduce_b200/libwc_exp_$v.so timeout 100 python bench.py --no-cpu-baseline --no-e2e --steps 10 --warmup 3 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$v', d['value'], d['ms_per_step'])"; done
-WC_LIB=$PWD/cuda-mapreduce_b200/libwc_exp_prof.so timeout 100 python tools/prof_probe.py 2>&1 | tail -1
+set -x
+python bench.py --no-cpu-baseline --steps 5 --warmup 3 > gpurun_out/b10.log 2>&1 && timeout 300 ncu --set full --clock-control none --import-source on -k regex:count_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r1_v11 -f python bench.py --no-cpu-baseline --no-e2e --steps 1 --warmup 3 > gpurun_out/ncu10.log 2>&1
+tail -1 gpurun_out/b10.log
