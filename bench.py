@@ -173,6 +173,8 @@ def main():
     ap.add_argument("--table-log2", type=int, default=0, help="override the word table size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
+                    help="N > 1: gather through NVLink peer memory (default) or the NCCL all-to-all protocol")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
@@ -215,6 +217,11 @@ def main():
     eng = pkg.Engine(device=local_rank, short_table_log2=wp["s_log2"], long_table_log2=wp["l_log2"], base_offset=lo,
                      path={"auto": 0, "hash": 1, "sort": 2}[args.path])
     ext = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local_rank))
+    # N > 1: table entries go to rank 0 through NVLink peer memory (wc_peer_*), one kernel per sender and
+    # a one-word all-reduce as the barrier; --exchange nccl uses the all-to-all protocol instead.
+    gather = None
+    if world > 1 and args.exchange == "peer":
+        gather = multi.PeerGather(eng, torch.device("cuda", local_rank), 1 << wp["s_log2"], 1 << wp["l_log2"], 64 << 20)
 
     def barrier():
         torch.cuda.synchronize()
@@ -231,7 +238,7 @@ def main():
             eng.aggregate()  # radix sort + run reduce: the sort path's counterpart of the hash tables
         if world > 1:  # key-owner exchange: NCCL all-to-all, owner reduce, gather on rank 0
             with torch.cuda.stream(ext):
-                multi.exchange_and_gather(eng, devt)
+                gather.run() if gather else multi.exchange_and_gather(eng, devt)
 
     # ---- value: device-resident, CUDA events on the launching stream
     for _ in range(args.warmup):
@@ -284,7 +291,7 @@ def main():
         eng.feed((host.data_ptr(), nbytes))
         if world > 1:
             with torch.cuda.stream(ext):
-                _, is_root = multi.exchange_and_gather(eng, devt)
+                _, is_root = gather.run() if gather else multi.exchange_and_gather(eng, devt)
             if not is_root:
                 eng.sync()
                 return None
@@ -319,7 +326,8 @@ def main():
                    "words_9B_plus": res.stats["n_long_words"],
                    "l2": "input (1e9 B) is larger than the 126 MB L2, every step re-reads it from HBM",
                    "step": "wc_reset (table memset) + tokenize/count kernel + roll-back/summary kernel"
-                           + (" + key-owner exchange (NCCL all-to-all, owner reduce, gather on rank 0)" if world > 1 else ""),
+                           + ((" + gather on rank 0 through NVLink peer memory (one push kernel per sender, one-word NCCL all-reduce as barrier)"
+                              if gather else " + key-owner exchange (NCCL all-to-all, owner reduce, gather on rank 0)") if world > 1 else ""),
                    "vocab_seed": corpus.vocab_seed, "text_seed": corpus.text_seed},
         "words_per_s": all_words / (ms_step * 1e-3),
         "frac_of_hbm_nominal_8TBs": value / world / 8000.0,
@@ -344,5 +352,17 @@ def main():
     print(json.dumps(line), flush=True)
 
 
+def _main_and_cleanup():
+    try:
+        main()
+    finally:
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                dist.destroy_process_group()
+        except Exception:
+            pass
+
+
 if __name__ == "__main__":
-    main()
+    _main_and_cleanup()

@@ -60,6 +60,18 @@ struct wc_engine {
     void *d_fin = nullptr, *h_fin = nullptr; // wc_finish: the used table entries, compacted (device / pinned host)
     size_t d_fin_cap = 0, h_fin_cap = 0;
     u64 finish_d2h = 0;                      // bytes the last wc_finish brought to the host
+
+    // peer gather (wc_peer_*): the root owns `area`; the others hold a mapping of it
+    struct Peer {
+        uint8_t *area = nullptr;   // root: cudaMalloc'd landing areas, one per rank
+        uint8_t *mapped = nullptr; // sender: the root's area in this process (IPC mapping or the same pointer)
+        bool ipc = false;
+        u32 n_ranks = 0, root_rank = 0, my_rank = 0;
+        u64 cap_words = 0, cap_long = 0, cap_blob = 0, stride = 0;
+        u64 seq = 0;               // pushes made / pulls made
+        u64 *d_cur = nullptr;      // sender: the push kernel's cursors
+        wc::PeerHeader *h_hdr = nullptr; // root: pinned copy of the headers
+    } peer;
     void *d_ord = nullptr;                   // wc_finish: sort keys and cub scratch
     size_t d_ord_cap = 0;
     bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
@@ -167,6 +179,10 @@ void wc_destroy(wc_engine *e) {
     if (e->d_status) cudaFree(e->d_status);
     if (e->d_ws) cudaFree(e->d_ws);
     if (e->d_cursors) cudaFree(e->d_cursors);
+    if (e->peer.area) cudaFree(e->peer.area);
+    if (e->peer.mapped && e->peer.ipc) cudaIpcCloseMemHandle(e->peer.mapped);
+    if (e->peer.d_cur) cudaFree(e->peer.d_cur);
+    if (e->peer.h_hdr) cudaFreeHost(e->peer.h_hdr);
     if (e->d_fin) cudaFree(e->d_fin);
     if (e->d_ord) cudaFree(e->d_ord);
     if (e->h_fin) cudaFreeHost(e->h_fin);
@@ -838,6 +854,13 @@ static int ensure_cursors(wc_engine *e) {
 
 extern "C" {
 
+int wc_set_base_offset(wc_engine *e, uint64_t base_offset) {
+    if (!e) return WC_ERR_INVALID;
+    if (e->fed != 0 || e->consumed != 0) { e->err = "wc_set_base_offset after input was fed"; return WC_ERR_INVALID; }
+    e->cfg.base_offset = base_offset;
+    return WC_OK;
+}
+
 int wc_shard_stats_get(wc_engine *e, wc_shard_stats *out) {
     if (!e || !out) return WC_ERR_INVALID;
     CK(cudaSetDevice(e->device));
@@ -979,6 +1002,155 @@ int wc_import_long(wc_engine *e, const void *dev_meta, uint64_t n_entries, const
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(e->stream));
     e->launches += 1;
+    return WC_OK;
+}
+
+// ---- peer gather: entries written straight into the root GPU's memory over NVLink (wc_shuffle.cuh)
+
+static u64 peer_stride(u64 cap_words, u64 cap_long, u64 cap_blob) {
+    return align_up(sizeof(wc::PeerHeader) + cap_words * sizeof(wc::WordRecord) + cap_long * sizeof(wc::LongRecord) +
+                        align_up(cap_blob, 8), 256);
+}
+
+static wc::PeerArea peer_area(uint8_t *base, const wc_engine::Peer &p, u32 rank) {
+    uint8_t *a = base + (u64)rank * p.stride;
+    wc::PeerArea A;
+    A.hdr = (wc::PeerHeader *)a;
+    A.words = (wc::WordRecord *)(a + sizeof(wc::PeerHeader));
+    A.longs = (wc::LongRecord *)(a + sizeof(wc::PeerHeader) + p.cap_words * sizeof(wc::WordRecord));
+    A.blob = (u64 *)(a + sizeof(wc::PeerHeader) + p.cap_words * sizeof(wc::WordRecord) + p.cap_long * sizeof(wc::LongRecord));
+    A.cap_words = p.cap_words; A.cap_long = p.cap_long; A.cap_blob_units = p.cap_blob / 8;
+    return A;
+}
+
+int wc_peer_root_create(wc_engine *e, uint32_t n_ranks, uint32_t root_rank, uint64_t words_per_rank, uint64_t long_per_rank,
+                        uint64_t blob_bytes_per_rank, void *handle_out) {
+    if (!e || n_ranks == 0 || n_ranks > kMaxParts || root_rank >= n_ranks || words_per_rank == 0) return WC_ERR_INVALID;
+    if (e->peer.area || e->peer.mapped) { e->err = "peer gather is already set up on this engine"; return WC_ERR_INVALID; }
+    CK(cudaSetDevice(e->device));
+    wc_engine::Peer p;
+    p.n_ranks = n_ranks; p.root_rank = root_rank; p.my_rank = root_rank;
+    p.cap_words = words_per_rank; p.cap_long = long_per_rank; p.cap_blob = align_up(blob_bytes_per_rank, 8);
+    p.stride = peer_stride(p.cap_words, p.cap_long, p.cap_blob);
+    CK(cudaMalloc((void **)&p.area, p.stride * n_ranks));
+    CK(cudaMemset(p.area, 0, p.stride * n_ranks));
+    CK(cudaMallocHost((void **)&p.h_hdr, sizeof(wc::PeerHeader) * n_ranks));
+    if (handle_out) {
+        static_assert(sizeof(cudaIpcMemHandle_t) == WC_PEER_HANDLE_BYTES, "handle size");
+        cudaIpcMemHandle_t h;
+        CK(cudaIpcGetMemHandle(&h, p.area));
+        memcpy(handle_out, &h, sizeof(h));
+    }
+    e->peer = p;
+    return WC_OK;
+}
+
+static int peer_sender_init(wc_engine *e, uint32_t my_rank, uint32_t n_ranks, uint32_t root_rank, uint64_t words_per_rank,
+                            uint64_t long_per_rank, uint64_t blob_bytes_per_rank) {
+    if (n_ranks == 0 || n_ranks > kMaxParts || my_rank >= n_ranks || root_rank >= n_ranks || my_rank == root_rank)
+        return WC_ERR_INVALID;
+    if (e->peer.area || e->peer.mapped) { e->err = "peer gather is already set up on this engine"; return WC_ERR_INVALID; }
+    wc_engine::Peer &p = e->peer;
+    p.n_ranks = n_ranks; p.root_rank = root_rank; p.my_rank = my_rank;
+    p.cap_words = words_per_rank; p.cap_long = long_per_rank; p.cap_blob = align_up(blob_bytes_per_rank, 8);
+    p.stride = peer_stride(p.cap_words, p.cap_long, p.cap_blob);
+    CK(cudaMalloc((void **)&p.d_cur, 4 * sizeof(u64)));
+    return WC_OK;
+}
+
+int wc_peer_open(wc_engine *e, uint32_t my_rank, uint32_t n_ranks, uint32_t root_rank, uint64_t words_per_rank,
+                 uint64_t long_per_rank, uint64_t blob_bytes_per_rank, const void *handle) {
+    if (!e || !handle) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    int rc = peer_sender_init(e, my_rank, n_ranks, root_rank, words_per_rank, long_per_rank, blob_bytes_per_rank);
+    if (rc != WC_OK) return rc;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void *ptr = nullptr;
+    CK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    e->peer.mapped = (uint8_t *)ptr; e->peer.ipc = true;
+    return WC_OK;
+}
+
+int wc_peer_attach(wc_engine *e, uint32_t my_rank, wc_engine *root) {
+    if (!e || !root || e == root || !root->peer.area) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    const wc_engine::Peer &r = root->peer;
+    int rc = peer_sender_init(e, my_rank, r.n_ranks, r.root_rank, r.cap_words, r.cap_long, r.cap_blob);
+    if (rc != WC_OK) return rc;
+    if (root->device != e->device) {
+        int can = 0;
+        CK(cudaDeviceCanAccessPeer(&can, e->device, root->device));
+        if (!can) { e->err = "no peer access to the root's GPU"; return WC_ERR_CUDA; }
+        cudaError_t pe = cudaDeviceEnablePeerAccess(root->device, 0);
+        if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) CK(pe);
+        (void)cudaGetLastError();
+    }
+    e->peer.mapped = r.area; e->peer.ipc = false;
+    return WC_OK;
+}
+
+int wc_peer_push(wc_engine *e, void *dev_flag) {
+    if (!e || !e->peer.mapped) return WC_ERR_INVALID;
+    if (e->sort_mode) { e->err = "peer gather needs the hash path"; return WC_ERR_INVALID; }
+    CK(cudaSetDevice(e->device));
+    int rc = wc_end_input(e);
+    if (rc != WC_OK) return rc;
+    const wc_engine::Peer &p = e->peer;
+    CK(cudaMemsetAsync(p.d_cur, 0, 4 * sizeof(u64), e->stream));
+    e->peer.seq++;
+    wc::peer_push_kernel<<<e->num_sms * 2, 256, 0, e->stream>>>(e->T, peer_area(p.mapped, p, p.my_rank), e->cfg.base_offset,
+                                                               e->consumed, e->peer.seq, p.d_cur, (u32 *)dev_flag);
+    CK(cudaGetLastError());
+    e->launches += 1;
+    return WC_OK;
+}
+
+int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
+    if (!e || !e->peer.area) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    wc_engine::Peer &p = e->peer;
+    p.seq++;
+    wc_shard_stats mine;
+    int rc = wc_shard_stats_get(e, &mine); // (drains this engine's stream: the caller's barrier is behind us)
+    if (rc != WC_OK) return rc;
+    CK(cudaMemcpy2DAsync(p.h_hdr, sizeof(wc::PeerHeader), p.area, p.stride, sizeof(wc::PeerHeader), p.n_ranks,
+                         cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    std::vector<wc_shard_stats> shards(p.n_ranks);
+    for (u32 r = 0; r < p.n_ranks; r++) {
+        if (r == p.root_rank) { shards[r] = mine; continue; }
+        const wc::PeerHeader &h = p.h_hdr[r];
+        if (h.seq != p.seq) { e->err = "peer gather: a rank's push has not arrived (call after the ranks' barrier)"; return WC_ERR_INVALID; }
+        if (h.flags) { e->err = "peer gather: a sender's tables or its landing area overflowed"; return WC_ERR_TABLE_FULL; }
+        wc_shard_stats s;
+        memset(&s, 0, sizeof(s));
+        s.base = h.base; s.bytes = h.bytes; s.n_flush = h.n_flush; s.n_empty = h.n_empty; s.lost_empty = h.lost_empty;
+        s.p0 = h.p0; s.stop = h.stop; s.p0_found = (u32)h.p0_found;
+        shards[r] = s;
+    }
+    wc_shard_stats job;
+    rc = wc_shard_stats_reduce(shards.data(), shards.size(), &job);
+    if (rc != WC_OK) { e->err = "peer gather: the ranks' shards do not tile the input"; return rc; }
+    auto dead = [&job](const wc_shard_stats &s) { return job.stop != ~0ull && s.base >= job.stop && s.bytes > 0; };
+    if (dead(mine)) { rc = wc_clear_tables(e); if (rc != WC_OK) return rc; }
+    for (u32 r = 0; r < p.n_ranks; r++) {
+        if (r == p.root_rank || dead(shards[r])) continue;
+        const wc::PeerHeader &h = p.h_hdr[r];
+        const wc::PeerArea A = peer_area(p.area, p, r);
+        if (h.n_words) {
+            wc::import_words_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, A.words, h.n_words);
+            e->launches += 1;
+        }
+        if (h.n_long) {
+            wc::import_long_kernel<<<e->num_sms, 256, 0, e->stream>>>(e->T, A.longs, h.n_long, (const uint8_t *)A.blob);
+            e->launches += 1;
+        }
+    }
+    CK(cudaGetLastError());
+    rc = wc_shard_stats_set(e, &job);
+    if (rc != WC_OK) return rc;
+    if (job_out) *job_out = job;
     return WC_OK;
 }
 

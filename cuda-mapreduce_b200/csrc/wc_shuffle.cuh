@@ -94,6 +94,79 @@ __global__ void rehash_words_kernel(Tables T, const ulonglong2 *old_keys, const 
     }
 }
 
+// ---- peer gather (one node, NVLink): every non-root GPU writes its table entries straight into a
+// landing area in the ROOT GPU's memory, mapped into its address space through CUDA IPC.  No staging
+// buffer, no size exchange: the stores travel over NVLink while the scan of the table is still going.
+// One area per sending rank: [PeerHeader][word records][long records][blob].
+struct PeerHeader {          // 256 bytes, written last (by the last block of the push kernel)
+    u64 n_words, n_long, blob_bytes;
+    u64 flags;               // bit 0: an area was too small; bits 8..: the sender's Status.err; bit 1: overflow log not empty
+    u64 base, bytes, n_flush, n_empty, lost_empty, p0, stop, p0_found; // the sender's shard counters
+    u64 seq;                 // the push number (the root checks it against its pull number)
+    u64 pad[19];
+};
+static_assert(sizeof(PeerHeader) == 256, "header size");
+struct PeerArea { PeerHeader *hdr; WordRecord *words; LongRecord *longs; u64 *blob; u64 cap_words, cap_long, cap_blob_units; };
+
+// cur (local, zeroed): [0] word records, [1] long records, [2] blob bytes, [3] blocks done
+__global__ void peer_push_kernel(Tables T, PeerArea A, u64 base, u64 bytes, u64 seq, u64 *cur, u32 *flag_out) {
+    const u32 lane = threadIdx.x & 31;
+    const u64 n_w = 1ull << T.w_log2, n_x = 1ull << T.x_log2;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 i0 = (u64)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n_w; i0 += stride) { // warp-uniform trip count
+        const u64 i = i0 + lane;
+        ulonglong2 k = make_ulonglong2(0, 0);
+        u64 c = 0;
+        if (i < n_w) { k = T.w_keys[i]; c = T.w_counts[i]; }
+        const bool used = k.x != 0 && c != 0;
+        const u32 m = __ballot_sync(0xFFFFFFFFu, used);
+        if (m == 0) continue;
+        u64 at = 0;
+        if (lane == 0) at = atomicAdd(&cur[0], (u64)__popc(m));
+        at = __shfl_sync(0xFFFFFFFFu, at, 0) + __popc(m & ((1u << lane) - 1));
+        if (used && at < A.cap_words) {
+            ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(&A.words[at]); // two 16-byte stores over NVLink
+            dst[0] = k;
+            dst[1] = make_ulonglong2(c, ~T.w_finv[i]);
+        }
+    }
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_x; i += stride) {
+        const u64 r = T.x_refs[i];
+        const u64 c = T.x_counts[i];
+        if (r == 0 || c == 0) continue;
+        const u64 unit = r & ((1ull << 40) - 1);
+        const u64 len = T.arena[unit], units = (len + 7) >> 3;
+        const u64 at = atomicAdd(&cur[1], 1ull);
+        const u64 off = atomicAdd(&cur[2], units * 8);
+        if (at < A.cap_long && (off >> 3) + units <= A.cap_blob_units) {
+            A.longs[at] = LongRecord{len, c, ~T.x_finv[i], off};
+            for (u64 j = 0; j < units; j++) A.blob[(off >> 3) + j] = T.arena[unit + 1 + j];
+        }
+    }
+    // the header goes last, after every block's records are on their way
+    __threadfence_system();
+    __shared__ u32 s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&cur[3], 1ull) == (u64)gridDim.x - 1;
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        __threadfence();
+        const u64 nw = atomicAdd(&cur[0], 0ull), nx = atomicAdd(&cur[1], 0ull), nb = atomicAdd(&cur[2], 0ull);
+        const Status *st = T.st;
+        u64 flags = (u64)st->err << 8;
+        if (nw > A.cap_words || nx > A.cap_long || (nb >> 3) > A.cap_blob_units) flags |= 1;
+        if (st->ovf_count != 0) flags |= 2;
+        PeerHeader h;
+        h.n_words = nw; h.n_long = nx; h.blob_bytes = nb; h.flags = flags;
+        h.base = base; h.bytes = bytes; h.n_flush = st->n_flush; h.n_empty = st->n_empty; h.lost_empty = st->lost_empty;
+        h.p0 = st->p0; h.stop = st->stop; h.p0_found = st->p0_found; h.seq = seq;
+        for (int q = 0; q < 19; q++) h.pad[q] = 0;
+        *A.hdr = h;
+        if (flag_out != nullptr) *flag_out = flags != 0;
+        __threadfence_system();
+    }
+}
+
 // wc_finish: sort keys for the exported records, so that the host reduce starts from sorted lists.
 // Record index space: word record i -> i, long record j -> n_w_max + j.  hi/lo = the word's first 16
 // bytes as two big-endian integers (zero padded), fst = its first offset.  Slots past the number of

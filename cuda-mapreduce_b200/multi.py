@@ -64,66 +64,160 @@ def reduce_stats(shards):
     return job
 
 
-def _a2a(send, send_counts, device):
-    """all_to_all of variable-size byte buffers; returns (recv buffer, recv byte counts)."""
+def _a2a(send, send_counts, recv_counts, device):
+    """all_to_all of variable-size byte buffers whose sizes both sides already know."""
+    recv = torch.empty(max(sum(recv_counts), 1), dtype=torch.uint8, device=device)[: sum(recv_counts)]
+    dist.all_to_all_single(recv, send[: sum(send_counts)], output_split_sizes=list(recv_counts),
+                           input_split_sizes=list(send_counts))
+    return recv
+
+
+def _gather_ints(vals, device):
+    """Every rank's list of integers on every rank: [world][len(vals)]."""
     world = dist.get_world_size()
-    sc = torch.tensor(send_counts, dtype=torch.int64, device=device)
-    rc = torch.empty(world, dtype=torch.int64, device=device)
-    dist.all_to_all_single(rc, sc)
-    rcl = rc.tolist()
-    recv = torch.empty(max(sum(rcl), 1), dtype=torch.uint8, device=device)[: sum(rcl)]
-    dist.all_to_all_single(recv, send[: sum(send_counts)], output_split_sizes=rcl, input_split_sizes=list(send_counts))
-    return recv, rcl
+    mine = torch.tensor([v if v < (1 << 63) else v - (1 << 64) for v in vals], dtype=torch.int64, device=device)
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    return [p.tolist() for p in parts]
 
 
-def exchange_and_gather(engine, device, root=0):
-    """Runs steps 1-5 of the multi-GPU protocol (include/wc.h).  Returns (job_stats, is_root); on the
-    root the engine then holds the whole job's tables and counters and wc_finish gives the rows."""
+# Below this many table entries in the whole job, every rank sends its entries straight to the root
+# (one collective); above it they are first reduced on their key owners, so that the root receives
+# each distinct word once instead of once per rank.
+DIRECT_GATHER_MAX_RECORDS = 2_000_000
+
+
+def exchange_and_gather(engine, device, root=0, mode="auto"):
+    """Runs the multi-GPU protocol (include/wc.h).  Returns (job_stats, is_root); on the root the
+    engine then holds the whole job's tables and counters and wc_finish gives the rows.
+
+    One all-gather tells every rank every shard's counters and how many records each rank holds for
+    each key owner, so no later collective needs a size exchange.  mode: "auto", "direct" (entries go
+    straight to the root) or "owner" (all-to-all by key owner, owner reduce, then gather)."""
     world, rank = dist.get_world_size(), dist.get_rank()
-    # 1. shard counters -> job counters; shards at or after STOP contribute nothing
+    # 1. shard counters and export sizes, once, to everybody
     mine = engine.shard_stats()
-    allst = [torch.empty(len(STAT_FIELDS), dtype=torch.int64, device=device) for _ in range(world)]
-    dist.all_gather(allst, stats_to_tensor(mine, device))
-    job = reduce_stats([tensor_to_stats(t) for t in allst])
-    if job.stop != NONE and mine.base >= job.stop and mine.bytes > 0:
-        engine.clear_tables()
-    # words of 17+ bytes leave through their own (small) buffers before the tables are cleared
     counts, n_long, long_bytes = engine.export_counts(world)
-    lmeta = torch.empty(max(n_long * REC, 1), dtype=torch.uint8, device=device)
-    lblob = torch.empty(max(long_bytes, 8), dtype=torch.uint8, device=device)
-    if n_long:
-        engine.export_long(lmeta.data_ptr(), lblob.data_ptr())
-    # 2. word records grouped by owner, all-to-all
-    offsets, acc = [], 0
-    for c in counts:
-        offsets.append(acc); acc += c
-    send = torch.empty(max(acc * REC, 1), dtype=torch.uint8, device=device)
-    if acc:
-        engine.export_words(world, offsets, send.data_ptr())
-    recv, rcl = _a2a(send, [c * REC for c in counts], device)
-    # 3. every word is now reduced on its owner
-    engine.clear_tables()
-    engine.import_words(recv.data_ptr(), sum(rcl) // REC)
-    # 4. gather the owners' tables (and the long words) on the root
-    owned, _, _ = engine.export_counts(1)
-    n_owned = owned[0]
-    out = torch.empty(max(n_owned * REC, 1), dtype=torch.uint8, device=device)
-    to_root = [0] * world
-    if rank != root and n_owned:
-        engine.export_words(1, [0], out.data_ptr())
-        to_root[root] = n_owned * REC
-    got, gcl = _a2a(out, to_root, device)
-    lm_send, lb_send = [0] * world, [0] * world
-    lm_send[root], lb_send[root] = n_long * REC, long_bytes
-    gmeta, gml = _a2a(lmeta, lm_send, device)
-    gblob, gbl = _a2a(lblob, lb_send, device)
+    nst = len(STAT_FIELDS)
+    table = _gather_ints([getattr(mine, f) for f in STAT_FIELDS] + list(counts) + [n_long, long_bytes], device)
+    shards = []
+    for row in table:
+        st = wc.ShardStats()
+        for f, v in zip(STAT_FIELDS, row[:nst]):
+            setattr(st, f, v & NONE)
+        shards.append(st)
+    job = reduce_stats(shards)
+    # a shard at or after STOP contributes nothing (the reference stopped reading before it)
+    dead = [job.stop != NONE and sh.base >= job.stop and sh.bytes > 0 for sh in shards]
+    per_owner = [[0 if dead[r] else c for c in table[r][nst:nst + world]] for r in range(world)]  # [sender][owner]
+    longs = [(0, 0) if dead[r] else (table[r][nst + world], table[r][nst + world + 1]) for r in range(world)]
+    if dead[rank]:
+        engine.clear_tables()
+        counts, n_long, long_bytes = [0] * world, 0, 0
+    total_records = sum(sum(r) for r in per_owner)
+    if mode == "auto":
+        mode = "direct" if total_records <= DIRECT_GATHER_MAX_RECORDS else "owner"
+
+    # words of 17+ bytes always travel straight to the root, in their own (small) buffers; they leave
+    # the tables before step 3 clears them (in "owner" mode the root's own come back in at the end)
+    any_long = any(n for n, _ in longs)
+    if any_long:
+        lmeta = torch.empty(max(n_long * REC, 1), dtype=torch.uint8, device=device)
+        lblob = torch.empty(max(long_bytes, 8), dtype=torch.uint8, device=device)
+        if n_long and (rank != root or mode == "owner"):
+            engine.export_long(lmeta.data_ptr(), lblob.data_ptr())
+
+    def to_root(nbytes_by_rank, buf):
+        """Every rank's buffer (its size known to all) to the root; the root's own stays where it is."""
+        send = [0] * world
+        if rank != root:
+            send[root] = nbytes_by_rank[rank]
+        recv = [nbytes_by_rank[r] if (rank == root and r != root) else 0 for r in range(world)]
+        return _a2a(buf, send, recv, device), recv
+
+    if mode == "direct":
+        # 2. each rank's entries, compacted, to the root; the root adds them to its own table
+        n_mine = sum(counts)
+        out = torch.empty(max(n_mine * REC, 1), dtype=torch.uint8, device=device)
+        if rank != root and n_mine:
+            engine.export_words(1, [0], out.data_ptr())
+        got, gcl = to_root([sum(r) * REC for r in per_owner], out)
+        if rank == root and sum(gcl):
+            engine.import_words(got.data_ptr(), sum(gcl) // REC)
+    else:
+        # 2. word records grouped by owner, all-to-all (sizes known from step 1)
+        offsets, acc = [], 0
+        for c in counts:
+            offsets.append(acc); acc += c
+        send = torch.empty(max(acc * REC, 1), dtype=torch.uint8, device=device)
+        if acc:
+            engine.export_words(world, offsets, send.data_ptr())
+        recv = _a2a(send, [c * REC for c in counts], [per_owner[r][rank] * REC for r in range(world)], device)
+        # 3. every word is now reduced on its owner
+        engine.clear_tables()
+        engine.import_words(recv.data_ptr(), recv.numel() // REC)
+        # 4. gather the owners' tables on the root
+        owned, _, _ = engine.export_counts(1)
+        owned_all = [r[0] for r in _gather_ints([owned[0]], device)]
+        out = torch.empty(max(owned[0] * REC, 1), dtype=torch.uint8, device=device)
+        if rank != root and owned[0]:
+            engine.export_words(1, [0], out.data_ptr())
+        got, gcl = to_root([n * REC for n in owned_all], out)
+        if rank == root and sum(gcl):
+            engine.import_words(got.data_ptr(), sum(gcl) // REC)
+
+    if any_long:
+        gmeta, gml = to_root([n * REC for n, _ in longs], lmeta)
+        gblob, gbl = to_root([b for _, b in longs], lblob)
+        if rank == root:
+            if mode == "owner" and n_long:
+                engine.import_long(lmeta.data_ptr(), n_long, lblob.data_ptr())
+            mo = bo = 0
+            for r in range(world):  # blob offsets are relative to each sender's blob
+                if gml[r]:
+                    engine.import_long(gmeta.data_ptr() + mo, gml[r] // REC, gblob.data_ptr() + bo)
+                mo += gml[r]; bo += gbl[r]
     if rank == root:
-        engine.import_words(got.data_ptr(), sum(gcl) // REC)
-        mo = bo = 0
-        for r in range(world):  # blob offsets are relative to each sender's blob
-            if gml[r]:
-                engine.import_long(gmeta.data_ptr() + mo, gml[r] // REC, gblob.data_ptr() + bo)
-            mo += gml[r]; bo += gbl[r]
-        # 5. the root's counters become the job's
-        engine.set_job_stats(job)
+        engine.set_job_stats(job)  # 5. the root's counters become the job's
     return job, rank == root
+
+
+class PeerGather:
+    """Single-node gather over NVLink peer memory (include/wc.h, wc_peer_*): set up once per engine,
+    then one call per job.  Every non-root rank stores its table entries and shard counters straight
+    into the root GPU's memory with one kernel; a one-word NCCL all-reduce behind that kernel is both
+    the barrier and the "any sender overflowed?" vote; the root then adds what arrived to its tables.
+    If a sender did overflow, all ranks fall back to exchange_and_gather() together."""
+
+    def __init__(self, engine, device, words_per_rank, long_per_rank, blob_bytes_per_rank, root=0):
+        self.engine, self.device, self.root = engine, device, root
+        world, rank = dist.get_world_size(), dist.get_rank()
+        caps = (words_per_rank, long_per_rank, blob_bytes_per_rank)
+        handle = torch.zeros(64, dtype=torch.uint8, device=device)
+        if rank == root:
+            raw = engine.peer_root_create(world, root, *caps)
+            handle.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+        dist.broadcast(handle, src=root)
+        if rank != root:
+            engine.peer_open(rank, world, root, *caps, bytes(handle.cpu().numpy().tobytes()))
+        self.flag = torch.zeros(1, dtype=torch.int32, device=device)
+        dist.barrier()
+
+    def run(self):
+        """Call on the engine's stream (torch.cuda.stream(ExternalStream(engine.stream()))).
+        Returns (job_stats or None, is_root)."""
+        rank = dist.get_rank()
+        self.flag.zero_()
+        if rank != self.root:
+            self.engine.peer_push(self.flag.data_ptr())
+        dist.all_reduce(self.flag, op=dist.ReduceOp.MAX)  # behind the push on this stream: barrier + vote
+        if int(self.flag.item()) != 0:  # every rank reads the vote, so that all of them take the fallback together
+            if rank == self.root:
+                try:
+                    self.engine.peer_pull()  # keeps the push/pull numbering in step; refuses the flagged data
+                except wc.WcError:
+                    pass
+            return exchange_and_gather(self.engine, self.device, self.root, mode="owner")
+        if rank != self.root:
+            return None, False
+        return self.engine.peer_pull(), True

@@ -112,6 +112,7 @@ def lib():
     L.wc_debug_classify16.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.wc_debug_smem_slot.argtypes = [u64]
     L.wc_debug_smem_slot.restype = C.c_uint32
+    L.wc_set_base_offset.argtypes = [vp, u64]
     L.wc_shard_stats_get.argtypes = [vp, C.POINTER(ShardStats)]
     L.wc_shard_stats_reduce.argtypes = [C.POINTER(ShardStats), sz, C.POINTER(ShardStats)]
     L.wc_shard_stats_set.argtypes = [vp, C.POINTER(ShardStats)]
@@ -121,6 +122,11 @@ def lib():
     L.wc_export_long.argtypes = [vp, vp, vp]
     L.wc_import_words.argtypes = [vp, vp, u64]
     L.wc_import_long.argtypes = [vp, vp, u64, vp]
+    L.wc_peer_root_create.argtypes = [vp, C.c_uint32, C.c_uint32, u64, u64, u64, vp]
+    L.wc_peer_open.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, u64, u64, u64, vp]
+    L.wc_peer_attach.argtypes = [vp, C.c_uint32, vp]
+    L.wc_peer_push.argtypes = [vp, vp]
+    L.wc_peer_pull.argtypes = [vp, C.POINTER(ShardStats)]
     L.wc_key_owner.argtypes = [u64, u64, C.c_uint32]
     L.wc_key_owner.restype = C.c_uint32
     L.wc_count_device_static.argtypes = [C.c_int, vp, sz, vp, C.c_uint32, vp, C.c_uint32, vp, u64, vp, vp]
@@ -195,8 +201,10 @@ class Engine:
         if rc != 0:
             raise WcError(rc, lib().wc_last_error(self.h).decode())
 
-    def reset(self):
+    def reset(self, base_offset=None):
         self._ck(lib().wc_reset(self.h))
+        if base_offset is not None:
+            self._ck(lib().wc_set_base_offset(self.h, base_offset))
 
     def feed(self, data):
         """data: bytes / bytearray / numpy uint8 array / (address, nbytes)."""
@@ -254,6 +262,29 @@ class Engine:
 
     def import_long(self, dev_meta, n, dev_blob):
         self._ck(lib().wc_import_long(self.h, C.c_void_p(dev_meta), n, C.c_void_p(dev_blob)))
+
+    # ---- peer gather (include/wc.h): entries stored straight into the root GPU's memory
+    def peer_root_create(self, n_ranks, root_rank, words_per_rank, long_per_rank, blob_bytes_per_rank):
+        handle = (C.c_uint8 * 64)()
+        self._ck(lib().wc_peer_root_create(self.h, n_ranks, root_rank, words_per_rank, long_per_rank,
+                                           blob_bytes_per_rank, handle))
+        return bytes(handle)
+
+    def peer_open(self, my_rank, n_ranks, root_rank, words_per_rank, long_per_rank, blob_bytes_per_rank, handle):
+        buf = (C.c_uint8 * 64).from_buffer_copy(handle)
+        self._ck(lib().wc_peer_open(self.h, my_rank, n_ranks, root_rank, words_per_rank, long_per_rank,
+                                    blob_bytes_per_rank, buf))
+
+    def peer_attach(self, my_rank, root_engine):
+        self._ck(lib().wc_peer_attach(self.h, my_rank, root_engine.h))
+
+    def peer_push(self, dev_flag_ptr=None):
+        self._ck(lib().wc_peer_push(self.h, C.c_void_p(dev_flag_ptr) if dev_flag_ptr else None))
+
+    def peer_pull(self):
+        job = ShardStats()
+        self._ck(lib().wc_peer_pull(self.h, C.byref(job)))
+        return job
 
     def finish_d2h_bytes(self):
         return lib().wc_finish_d2h_bytes(self.h)

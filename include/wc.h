@@ -181,6 +181,9 @@ typedef struct wc_shard_stats {
 } wc_shard_stats;
 #define WC_WORD_RECORD_BYTES 32
 #define WC_LONG_RECORD_BYTES 32
+/* Where this engine's byte range begins in the whole input (wc_config.base_offset), for the next
+ * job of an engine that is reused for another shard.  Only right after wc_create / wc_reset. */
+WC_API int wc_set_base_offset(wc_engine *e, uint64_t base_offset);
 WC_API int wc_shard_stats_get(wc_engine *e, wc_shard_stats *out);
 WC_API int wc_shard_stats_reduce(const wc_shard_stats *shards, size_t n, wc_shard_stats *job);
 WC_API int wc_shard_stats_set(wc_engine *e, const wc_shard_stats *job);
@@ -192,6 +195,30 @@ WC_API int wc_export_long(wc_engine *e, void *dev_meta, void *dev_blob);
 WC_API int wc_import_words(wc_engine *e, const void *dev_records, uint64_t n_records);
 WC_API int wc_import_long(wc_engine *e, const void *dev_meta, uint64_t n_entries, const void *dev_blob);
 WC_API uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts);
+
+/* ---- peer gather: steps 2-5 above in one kernel per sender, over NVLink peer memory ------------------
+ *
+ * No reference counterpart (one GPU, main.cu:133-162).  For GPUs of ONE node.  The gathering ("root")
+ * engine owns a landing area in its GPU's memory with one slot per rank; every other engine maps it
+ * (CUDA IPC between processes, or directly inside one process) and wc_peer_push() scans its tables
+ * once, storing each used entry -- and, last, a header with its shard counters -- straight into its
+ * slot on the root GPU.  No staging buffer and no size exchange; the stores cross NVLink while the
+ * scan is still running.  After a barrier between the ranks (the caller's: any stream-ordered
+ * collective behind the push, e.g. a one-word NCCL all-reduce), wc_peer_pull() on the root reduces
+ * the shard counters, adds the entries of every rank that lies before the job's STOP to its own
+ * tables and installs the job counters; wc_finish() then gives the rows.
+ * Slots are sized by the caller (a slot of words_per_rank = the sender's table size can never
+ * overflow); a sender whose tables overflowed says so in its header and wc_peer_pull() fails with
+ * WC_ERR_TABLE_FULL -- fall back to the exchange above.  dev_flag (optional, device memory, 4 bytes)
+ * receives 1 if this sender has such a problem, for callers that fold it into their barrier. */
+#define WC_PEER_HANDLE_BYTES 64
+WC_API int wc_peer_root_create(wc_engine *root, uint32_t n_ranks, uint32_t root_rank, uint64_t words_per_rank,
+                               uint64_t long_per_rank, uint64_t blob_bytes_per_rank, void *handle_out);
+WC_API int wc_peer_open(wc_engine *e, uint32_t my_rank, uint32_t n_ranks, uint32_t root_rank, uint64_t words_per_rank,
+                        uint64_t long_per_rank, uint64_t blob_bytes_per_rank, const void *handle);
+WC_API int wc_peer_attach(wc_engine *e, uint32_t my_rank, wc_engine *root); /* same process */
+WC_API int wc_peer_push(wc_engine *e, void *dev_flag);                      /* asynchronous, on the engine's stream */
+WC_API int wc_peer_pull(wc_engine *root, wc_shard_stats *job_out);
 
 /* ---- wc_count_device_static: counting without any allocation -------------------------------
  *

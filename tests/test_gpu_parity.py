@@ -360,6 +360,52 @@ def test_key_owner_exchange_two_engines_one_gpu(pkg):
                (exp.n_flush, exp.n_empty, exp.n_lost_empty, exp.stop)
 
 
+def test_peer_gather_three_engines_one_gpu(pkg):
+    """wc_peer_*: the senders' kernels store their table entries and shard counters straight into the
+    root engine's landing area (on a multi-GPU node: over NVLink through a CUDA IPC mapping; here three
+    engines of one process on this one GPU, attached directly).  Same engines for several jobs in a
+    row: the push/pull numbering and the landing areas are reused."""
+    from cuda_mapreduce_b200 import multi
+    rng = random.Random(21)
+    body = random_text(rng, 150000, weird=0.0).replace(b"\n\n", b"\n")
+    long_words = b" ".join(bytes(rng.choice(b"abcdefgh") for _ in range(rng.randint(17, 60))) for _ in range(50))
+    k2 = body.index(b"\n", len(body) * 4 // 5) + 1
+    texts = [
+        body + b" " + long_words + b"\n" + body[:3000],
+        b"  \n \n" + body[:50000] + long_words + b"\n",   # leading empty words: lost until the first real word
+        body[:40000] + b"\n\n" + body[40000:],               # STOP inside the first shard: the others are dead
+        body[:k2] + b"\n" + body[k2:],                        # STOP inside the last shard
+        body,
+    ]
+    world = 3
+    engs = [pkg.Engine(chunk_bytes=1 << 20, **SMALL) for _ in range(world)]
+    try:
+        engs[0].peer_root_create(world, 0, 1 << SMALL["short_table_log2"], 1 << SMALL["long_table_log2"],
+                                 SMALL["arena_bytes"])
+        for r in (1, 2):
+            engs[r].peer_attach(r, engs[0])
+        for data in texts:
+            cuts = multi.line_aligned_cuts(data, world)
+            for r, e in enumerate(engs):
+                e.reset(base_offset=cuts[r])
+                e.feed(data[cuts[r]:cuts[r + 1]])
+            for e in engs[1:]:
+                e.peer_push()
+            for e in engs[1:]:
+                e.sync()                                   # (stands for the ranks' barrier)
+            job = engs[0].peer_pull()
+            got = engs[0].finish()
+            exp = O.fast(data)
+            assert got.pairs() == exp.pairs() and got.total == exp.total
+            assert got.firsts == [f for _, _, f in exp.rows]
+            assert (got.stats["n_flush"], got.stats["n_empty"], got.stats["n_lost_empty"], got.stats["stop"]) == \
+                (exp.n_flush, exp.n_empty, exp.n_lost_empty, exp.stop)
+            assert job.bytes == len(data)
+    finally:
+        for e in engs:
+            e.close()
+
+
 def test_word_table_grows_instead_of_overflowing(pkg):
     """A word table far too small for the vocabulary: words it cannot take go to the overflow log, the
     host re-hashes into a larger table and replays the log -- nothing is lost (wc_engine.cu

@@ -105,7 +105,7 @@ class HostEngine:
             self._add(w, c, f)
 
 
-def _worker(rank, world, port, data, q):
+def _worker(rank, world, port, data, q, mode):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     pkg = load_pkg()
@@ -113,7 +113,7 @@ def _worker(rank, world, port, data, q):
     cuts = multi.line_aligned_cuts(data, world)
     lo, hi = cuts[rank], cuts[rank + 1]
     eng = HostEngine(pkg, data[lo:hi], lo)
-    job, is_root = multi.exchange_and_gather(eng, torch.device("cpu"))
+    job, is_root = multi.exchange_and_gather(eng, torch.device("cpu"), mode=mode)
     if is_root:
         words = sorted(eng.words.items(), key=lambda kv: kv[1][1])
         res = pkg.wc.debug_finalize([w for w, _ in words], [v[0] for _, v in words], [v[1] for _, v in words],
@@ -123,13 +123,13 @@ def _worker(rank, world, port, data, q):
     dist.destroy_process_group()
 
 
-def run_world(data, world=2):
+def run_world(data, world=2, mode="auto"):
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, data, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, data, q, mode)) for r in range(world)]
     for p in procs:
         p.start()
     out = q.get(timeout=120)
@@ -139,13 +139,15 @@ def run_world(data, world=2):
     return out
 
 
-def check(data, world=2):
-    rows, total, n_flush, n_empty, stop, nbytes = run_world(data, world)
+def check(data, world=2, modes=("direct", "owner")):
+    """Both exchange protocols: entries straight to the root, and all-to-all by key owner first."""
     exp = O.fast(data)
-    assert rows == exp.pairs()
-    assert total == exp.total
-    assert (n_flush, n_empty) == (exp.n_flush, exp.n_empty)
-    assert (stop if stop != NONE else nbytes) == exp.stop and nbytes == len(data)
+    for mode in modes:
+        rows, total, n_flush, n_empty, stop, nbytes = run_world(data, world, mode)
+        assert rows == exp.pairs(), mode
+        assert total == exp.total
+        assert (n_flush, n_empty) == (exp.n_flush, exp.n_empty)
+        assert (stop if stop != NONE else nbytes) == exp.stop and nbytes == len(data)
 
 
 def test_two_ranks_plain_text():
@@ -164,10 +166,11 @@ def test_two_ranks_with_long_words_and_leading_empties():
 def test_two_ranks_stop_in_first_and_in_second_shard():
     rng = random.Random(43)
     body = random_text(rng, 3000, weird=0.0).replace(b"\n\n", b"\n")
-    check(body[:2000] + b"\n\n" + body[2000:])                       # blank line in shard 0: shard 1 is ignored
+    check(body[:2000] + b"\n\n" + body[2000:], modes=("owner",))     # blank line in shard 0: shard 1 is ignored
     k = body.index(b"\n", len(body) * 3 // 4) + 1
-    check(body[:k] + b"\n" + body[k:])                               # blank line in shard 1
-    check(b" \n" * 2000 + body)                                       # shard 0 holds only empty words
+    check(body[:k] + b"\n" + body[k:], modes=("direct",))            # blank line in shard 1
+    check(b" \n" * 2000 + body, modes=("owner",))                     # shard 0 holds only empty words
+    check(body[:2000] + b"\n\n" + body[2000:], modes=("direct",))
 
 
 def test_shard_planning_and_stats_reduce():

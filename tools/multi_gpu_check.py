@@ -42,14 +42,17 @@ def main():
     cases.append(("stop_in_a_later_shard", base[:k] + b"\n" + base[k:]))
     cases.append(("leading_empties_and_long_words", b"  \n" * 1000 + base + b" " + b"q" * 100 + b" " + b"w" * 5000 + b"\n" + base[:9999]))
     ok = True
-    for name, data in cases:
+    for name, data, mode in [(n, d, m) for (n, d) in cases for m in ("direct", "owner", "peer")]:
         cuts = multi.line_aligned_cuts(data, world)
         lo, hi = cuts[rank], cuts[rank + 1]
         with pkg.Engine(device=lr, base_offset=lo, short_table_log2=21, long_table_log2=12) as eng:
             eng.feed(data[lo:hi])
             ext = torch.cuda.ExternalStream(eng.stream(), device=dev)
             with torch.cuda.stream(ext):
-                job, is_root = multi.exchange_and_gather(eng, dev)
+                if mode == "peer":
+                    job, is_root = multi.PeerGather(eng, dev, 1 << 21, 1 << 12, 64 << 20).run()
+                else:
+                    job, is_root = multi.exchange_and_gather(eng, dev, mode=mode)
             if is_root:
                 got = eng.finish()
                 exp = orc.fast_mt(np.frombuffer(data, dtype=np.uint8))
@@ -58,7 +61,7 @@ def main():
                     (got.stats["n_flush"], got.stats["n_empty"], got.stats["n_lost_empty"], got.stats["stop"]) == \
                     (exp.n_flush, exp.n_empty, exp.n_lost_empty, exp.stop)
                 ok = ok and same
-                print(json.dumps({"case": name, "world": world, "bytes": len(data), "rows": got.n_rows,
+                print(json.dumps({"case": name, "exchange": mode, "world": world, "bytes": len(data), "rows": got.n_rows,
                                   "total": got.total, "bit_exact_vs_oracle": same}), flush=True)
             else:
                 eng.sync()
