@@ -1111,18 +1111,30 @@ int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
     CK(cudaSetDevice(e->device));
     wc_engine::Peer &p = e->peer;
     p.seq++;
-    wc_shard_stats mine;
-    int rc = wc_shard_stats_get(e, &mine); // (drains this engine's stream: the caller's barrier is behind us)
+    int rc = wc_end_input(e);
     if (rc != WC_OK) return rc;
+    // one wait for everything the host needs: this engine's counters and every sender's header
+    CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpy2DAsync(p.h_hdr, sizeof(wc::PeerHeader), p.area, p.stride, sizeof(wc::PeerHeader), p.n_ranks,
                          cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    wc_shard_stats mine;
+    if (e->h_status->ovf_count != 0 || e->h_status->err != 0) { // rare: grow the table / replay its overflow log first
+        rc = wc_shard_stats_get(e, &mine);
+        if (rc != WC_OK) return rc;
+    } else {
+        const wc::Status &st = *e->h_status;
+        memset(&mine, 0, sizeof(mine));
+        mine.base = e->cfg.base_offset; mine.bytes = e->consumed;
+        mine.n_flush = st.n_flush; mine.n_empty = st.n_empty; mine.lost_empty = st.lost_empty;
+        mine.p0 = st.p0; mine.p0_found = st.p0_found; mine.stop = st.stop;
+    }
     std::vector<wc_shard_stats> shards(p.n_ranks);
     for (u32 r = 0; r < p.n_ranks; r++) {
         if (r == p.root_rank) { shards[r] = mine; continue; }
         const wc::PeerHeader &h = p.h_hdr[r];
         if (h.seq != p.seq) { e->err = "peer gather: a rank's push has not arrived (call after the ranks' barrier)"; return WC_ERR_INVALID; }
-        if (h.flags) { e->err = "peer gather: a sender's tables or its landing area overflowed"; return WC_ERR_TABLE_FULL; }
+        if (h.flags) { e->err = "peer gather: a sender's tables or its landing area overflowed"; return WC_ERR_TOO_LARGE; }
         wc_shard_stats s;
         memset(&s, 0, sizeof(s));
         s.base = h.base; s.bytes = h.bytes; s.n_flush = h.n_flush; s.n_empty = h.n_empty; s.lost_empty = h.lost_empty;
@@ -1134,22 +1146,28 @@ int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
     if (rc != WC_OK) { e->err = "peer gather: the ranks' shards do not tile the input"; return rc; }
     auto dead = [&job](const wc_shard_stats &s) { return job.stop != ~0ull && s.base >= job.stop && s.bytes > 0; };
     if (dead(mine)) { rc = wc_clear_tables(e); if (rc != WC_OK) return rc; }
+    wc::ImportList L;
+    memset(&L, 0, sizeof(L));
     for (u32 r = 0; r < p.n_ranks; r++) {
         if (r == p.root_rank || dead(shards[r])) continue;
         const wc::PeerHeader &h = p.h_hdr[r];
+        if (h.n_words == 0 && h.n_long == 0) continue;
         const wc::PeerArea A = peer_area(p.area, p, r);
-        if (h.n_words) {
-            wc::import_words_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, A.words, h.n_words);
-            e->launches += 1;
-        }
-        if (h.n_long) {
-            wc::import_long_kernel<<<e->num_sms, 256, 0, e->stream>>>(e->T, A.longs, h.n_long, (const uint8_t *)A.blob);
-            e->launches += 1;
-        }
+        L.w[L.n] = A.words; L.n_w[L.n] = h.n_words;
+        L.x[L.n] = A.longs; L.n_x[L.n] = h.n_long;
+        L.blob[L.n] = (const uint8_t *)A.blob;
+        L.n++;
     }
+    if (L.n) {
+        wc::import_areas_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, L);
+        e->launches += 1;
+    }
+    // the root's counters become the job's (stream ordered; wc_finish reads them after its own sync)
+    wc::set_job_counters_kernel<<<1, 1, 0, e->stream>>>(e->d_status, job.n_flush, job.n_empty, job.lost_empty, job.p0, job.stop,
+                                                       job.p0_found);
     CK(cudaGetLastError());
-    rc = wc_shard_stats_set(e, &job);
-    if (rc != WC_OK) return rc;
+    e->launches += 1;
+    e->job_stats_set = true; e->job_bytes = job.bytes;
     if (job_out) *job_out = job;
     return WC_OK;
 }

@@ -167,6 +167,43 @@ __global__ void peer_push_kernel(Tables T, PeerArea A, u64 base, u64 bytes, u64 
     }
 }
 
+// The root's side: every live sender's records into the root's tables, in one launch.
+struct ImportList {
+    const WordRecord *w[64]; u64 n_w[64];
+    const LongRecord *x[64]; u64 n_x[64];
+    const uint8_t *blob[64];
+    u32 n;
+};
+__global__ void import_areas_kernel(Tables T, const __grid_constant__ ImportList L) {
+    u32 made_w = 0, made_x = 0;
+    const u64 tid = blockIdx.x * (u64)blockDim.x + threadIdx.x, stride = (u64)gridDim.x * blockDim.x;
+    for (u32 a = 0; a < L.n; a++) {
+        for (u64 i = tid; i < L.n_w[a]; i += stride) {
+            const WordRecord r = L.w[a][i];
+            if (r.k0 == 0 || r.count == 0) continue;
+            const u32 len = r.k1 ? 8 + key_len8(r.k1) : key_len8(r.k0);
+            made_w += word_insert(T, r.k0, r.k1, len, r.count, r.first);
+        }
+        for (u64 i = tid; i < L.n_x[a]; i += stride) {
+            const LongRecord r = L.x[a][i];
+            if (r.len == 0 || r.count == 0) continue;
+            made_x += long_insert(&T, L.blob[a], r.blob_off, r.len, r.count, r.first);
+        }
+    }
+    made_w = __reduce_add_sync(0xFFFFFFFFu, made_w);
+    made_x = __reduce_add_sync(0xFFFFFFFFu, made_x);
+    if ((threadIdx.x & 31) == 0) {
+        if (made_w) atomicAdd(&T.st->w_entries, (u64)made_w);
+        if (made_x) atomicAdd(&T.st->x_entries, (u64)made_x);
+    }
+}
+
+// Installs the job-wide counters without touching what the import kernels are updating.
+__global__ void set_job_counters_kernel(Status *st, u64 n_flush, u64 n_empty, u64 lost_empty, u64 p0, u64 stop, u32 p0_found) {
+    st->n_flush = n_flush; st->n_empty = n_empty; st->lost_empty = lost_empty; st->p0 = p0; st->stop = stop;
+    st->p0_found = p0_found;
+}
+
 // wc_finish: sort keys for the exported records, so that the host reduce starts from sorted lists.
 // Record index space: word record i -> i, long record j -> n_w_max + j.  hi/lo = the word's first 16
 // bytes as two big-endian integers (zero padded), fst = its first offset.  Slots past the number of

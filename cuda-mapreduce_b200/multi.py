@@ -211,13 +211,19 @@ class PeerGather:
         if rank != self.root:
             self.engine.peer_push(self.flag.data_ptr())
         dist.all_reduce(self.flag, op=dist.ReduceOp.MAX)  # behind the push on this stream: barrier + vote
-        if int(self.flag.item()) != 0:  # every rank reads the vote, so that all of them take the fallback together
-            if rank == self.root:
-                try:
-                    self.engine.peer_pull()  # keeps the push/pull numbering in step; refuses the flagged data
-                except wc.WcError:
-                    pass
+        # Every rank learns the vote, so that all of them take the fallback together: the senders read
+        # the flag, the root sees the same bits in the headers it pulls (one host wait instead of two).
+        job = None
+        if rank == self.root:
+            try:
+                job = self.engine.peer_pull()
+                bad = False
+            except wc.WcError as ex:
+                if ex.code != -7:  # WC_ERR_TOO_LARGE: a sender said its tables or its landing area overflowed
+                    raise
+                bad = True
+        else:
+            bad = int(self.flag.item()) != 0
+        if bad:
             return exchange_and_gather(self.engine, self.device, self.root, mode="owner")
-        if rank != self.root:
-            return None, False
-        return self.engine.peer_pull(), True
+        return job, rank == self.root

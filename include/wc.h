@@ -209,7 +209,7 @@ WC_API uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts);
  * tables and installs the job counters; wc_finish() then gives the rows.
  * Slots are sized by the caller (a slot of words_per_rank = the sender's table size can never
  * overflow); a sender whose tables overflowed says so in its header and wc_peer_pull() fails with
- * WC_ERR_TABLE_FULL -- fall back to the exchange above.  dev_flag (optional, device memory, 4 bytes)
+ * WC_ERR_TOO_LARGE -- fall back to the exchange above.  dev_flag (optional, device memory, 4 bytes)
  * receives 1 if this sender has such a problem, for callers that fold it into their barrier. */
 #define WC_PEER_HANDLE_BYTES 64
 WC_API int wc_peer_root_create(wc_engine *root, uint32_t n_ranks, uint32_t root_rank, uint64_t words_per_rank,
