@@ -19,6 +19,7 @@
 #include <chrono>
 #include <unordered_map>
 #include "wc_finalize.h"
+#include "wc_reduce.cuh"
 
 using wc::u32;
 using wc::u64;
@@ -74,6 +75,8 @@ struct wc_engine {
     } peer;
     void *d_ord = nullptr;                   // wc_finish: sort keys and cub scratch
     size_t d_ord_cap = 0;
+    void *d_fz = nullptr;                    // wc_finish: arrays of the device reduce (wc_reduce.cuh)
+    size_t d_fz_cap = 0;
     bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
     u64 job_bytes = 0;
 
@@ -185,6 +188,7 @@ void wc_destroy(wc_engine *e) {
     if (e->peer.h_hdr) cudaFreeHost(e->peer.h_hdr);
     if (e->d_fin) cudaFree(e->d_fin);
     if (e->d_ord) cudaFree(e->d_ord);
+    if (e->d_fz) cudaFree(e->d_fz);
     if (e->h_fin) cudaFreeHost(e->h_fin);
     if (e->so_key) { cudaFree(e->so_key); cudaFree(e->so_count); cudaFree(e->so_first); }
     if (e->em.cursor) cudaFree(e->em.cursor);
@@ -677,8 +681,13 @@ int wc_finish(wc_engine *e, wc_result **out) {
     const size_t blob_max = (size_t)st.arena_used * 8;
     const size_t n_ord = e->sort_mode ? 0 : n_w_max + n_x_max; // (sort mode adds its entries on the host: no device order)
     const size_t off_w = 64, off_x = off_w + n_w_max * sizeof(wc::WordRecord),
-                 off_b = off_x + n_x_max * sizeof(wc::LongRecord), off_pk = off_b + blob_max,
+                 off_b = off_x + n_x_max * sizeof(wc::LongRecord), off_ri = off_b + blob_max,
+                 off_rc = off_ri + align_up(n_ord * sizeof(u32), 8), off_pk = off_rc + n_ord * sizeof(u64),
                  off_pf = off_pk + align_up(n_ord * sizeof(u32), 8), need = off_pf + align_up(n_ord * sizeof(u32), 8);
+    // [cursors][word records][long records][blob][row record indices][row counts] go to the host;
+    // [by_key][by_first] only when the host does the reduce (WC_HOST_REDUCE=1, a cross-check)
+    static const bool host_reduce = getenv("WC_HOST_REDUCE") != nullptr;
+    const size_t copy_bytes = host_reduce ? need : off_pk;
     rc = ensure_cursors(e);
     if (rc != WC_OK) return rc;
     if (need > e->d_fin_cap) {
@@ -728,29 +737,143 @@ int wc_finish(wc_engine *e, wc_result **out) {
             (const wc::WordRecord *)(dfin + off_w), n_w_max, e->d_cursors + kMaxParts, (const wc::LongRecord *)(dfin + off_x),
             n_x_max, e->d_cursors + 2 * kMaxParts, (const u64 *)(dfin + off_b), hi, lo, fst, iota);
         size_t tbx = tb;
+        CK(cub::DeviceRadixSort::SortPairs(temp, tbx, (const u64 *)fst, k_out, (const u32 *)iota, (u32 *)(dfin + off_pf), n, 0,
+                                           64, e->stream));
+        tbx = tb;
         CK(cub::DeviceRadixSort::SortPairs(temp, tbx, (const u64 *)lo, k_out, (const u32 *)iota, by_lo, n, 0, 64, e->stream));
         wc::gather_u64_kernel<<<e->num_sms * 2, 256, 0, e->stream>>>(hi, by_lo, n_ord, hi2);
         tbx = tb;
         CK(cub::DeviceRadixSort::SortPairs(temp, tbx, (const u64 *)hi2, k_out, (const u32 *)by_lo, (u32 *)(dfin + off_pk), n, 0,
-                                           64, e->stream));
-        tbx = tb;
-        CK(cub::DeviceRadixSort::SortPairs(temp, tbx, (const u64 *)fst, k_out, (const u32 *)iota, (u32 *)(dfin + off_pf), n, 0,
-                                           64, e->stream));
+                                           64, e->stream)); // k_out = the sorted high halves
         CK(cudaGetLastError());
         e->launches += 5;
+
+        if (!host_reduce) {
+            // ---- the reduce itself (wc_reduce.cuh): owners by range-minimum queries in key order, counts
+            // to the owners, rows compacted in order of first occurrence
+            const size_t n1 = (n_ord + wc::kRmqBlock - 1) / wc::kRmqBlock, n2 = (n1 + wc::kRmqBlock - 1) / wc::kRmqBlock;
+            size_t tb_sel = 0;
+            CK(cub::DeviceSelect::Flagged(nullptr, tb_sel, (const u32 *)nullptr, (const unsigned char *)nullptr, (u32 *)nullptr,
+                                          (u64 *)nullptr, n, e->stream));
+            const size_t b1 = align_up(n1 * sizeof(u64), 256), b2 = align_up(n2 * sizeof(u64), 256);
+            const size_t need_fz = 3 * a8 + 3 * a4 + align_up(n_ord, 256) + 2 * b1 + 2 * b2 + align_up(tb_sel, 256) + 256;
+            if (need_fz > e->d_fz_cap) {
+                if (e->d_fz) cudaFree(e->d_fz);
+                e->d_fz = nullptr; e->d_fz_cap = 0;
+                CK(cudaMalloc(&e->d_fz, need_fz + need_fz / 4));
+                e->d_fz_cap = need_fz + need_fz / 4;
+            }
+            uint8_t *z = (uint8_t *)e->d_fz;
+            wc::ReduceArrays A;
+            A.w = (const wc::WordRecord *)(dfin + off_w); A.n_w_max = n_w_max; A.n_w_ptr = e->d_cursors + kMaxParts;
+            A.x = (const wc::LongRecord *)(dfin + off_x); A.n_x_max = n_x_max; A.n_x_ptr = e->d_cursors + 2 * kMaxParts;
+            A.blob = (const u64 *)(dfin + off_b);
+            A.by_key = (const u32 *)(dfin + off_pk); A.by_first = (const u32 *)(dfin + off_pf);
+            A.n = n_ord;
+            A.s_hi = k_out;
+            A.s_lo = hi2;                       // (free again after the last sort)
+            A.s_first = (u64 *)z; A.s_count = (u64 *)(z + a8); A.acc = (u64 *)(z + 2 * a8);
+            A.s_len = (u32 *)(z + 3 * a8); A.pos_of_idx = (u32 *)(z + 3 * a8 + a4); A.owner = (u32 *)(z + 3 * a8 + 2 * a4);
+            unsigned char *flags = z + 3 * a8 + 3 * a4;
+            uint8_t *zz = flags + align_up(n_ord, 256);
+            A.bmin1 = (u64 *)zz; A.bpos1 = (u32 *)(zz + b1); A.bmin2 = (u64 *)(zz + 2 * b1); A.bpos2 = (u32 *)(zz + 2 * b1 + b2);
+            void *sel_temp = zz + 2 * b1 + 2 * b2;
+            A.counters = (u64 *)(zz + 2 * b1 + 2 * b2 + align_up(tb_sel, 256));
+            CK(cudaMemsetAsync(A.counters, 0, 2 * sizeof(u64), e->stream));
+            const int gb = e->num_sms * 8;
+            wc::reduce_gather_kernel<<<gb, 256, 0, e->stream>>>(A, lo);
+            wc::reduce_blockmin_kernel<<<(unsigned)(n1 < 65535 ? n1 : 65535), wc::kRmqBlock, 0, e->stream>>>(A.s_first, nullptr, n_ord, A.bmin1, A.bpos1);
+            wc::reduce_blockmin_kernel<<<(unsigned)(n2 < 65535 ? n2 : 65535), wc::kRmqBlock, 0, e->stream>>>(A.bmin1, A.bpos1, n1, A.bmin2, A.bpos2);
+            wc::reduce_owner_kernel<<<gb, 256, 0, e->stream>>>(A, e->cfg.mode == WC_MODE_EXACT);
+            wc::reduce_rowflags_kernel<<<gb, 256, 0, e->stream>>>(A, flags);
+            size_t tbs = tb_sel;
+            CK(cub::DeviceSelect::Flagged(sel_temp, tbs, A.by_first, (const unsigned char *)flags, (u32 *)(dfin + off_ri),
+                                          A.counters + 1, n, e->stream));
+            wc::reduce_rowcounts_kernel<<<gb, 256, 0, e->stream>>>(A, (const u32 *)(dfin + off_ri), A.counters + 1,
+                                                                   (u64 *)(dfin + off_rc));
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(dfin + 24, A.counters, 2 * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
+            e->launches += 7;
+        }
     }
     // cursors into the head of the block: [0] word records, [1] long records, [2] blob bytes
     CK(cudaMemcpyAsync(dfin, e->d_cursors + kMaxParts, sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
     CK(cudaMemcpyAsync(dfin + 8, e->d_cursors + 2 * kMaxParts, 2 * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
-    CK(cudaMemcpyAsync(hfin, dfin, need, cudaMemcpyDeviceToHost, e->stream));
-    CK(cudaStreamSynchronize(e->stream));
-    e->finish_d2h = need + sizeof(wc::Status);
+    const bool device_reduce = n_ord > 1 && !host_reduce;
+    if (device_reduce) {
+        // rows are usually far fewer than entries: fetch the head first, then exactly the rows
+        CK(cudaMemcpyAsync(hfin, dfin, off_ri, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        const u64 n_rows = ((const u64 *)hfin)[4];
+        if (n_rows > n_ord) { e->err = "row counter is inconsistent"; return WC_ERR_CUDA; }
+        if (n_rows) {
+            CK(cudaMemcpyAsync(hfin + off_ri, dfin + off_ri, n_rows * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaMemcpyAsync(hfin + off_rc, dfin + off_rc, n_rows * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaStreamSynchronize(e->stream));
+        }
+        e->finish_d2h = off_ri + n_rows * 12 + sizeof(wc::Status);
+    } else {
+        CK(cudaMemcpyAsync(hfin, dfin, copy_bytes, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        e->finish_d2h = copy_bytes + sizeof(wc::Status);
+    }
     const double t_d2h = since();
     const u64 n_w = ((const u64 *)hfin)[0], n_x = ((const u64 *)hfin)[1];
     if (n_w > n_w_max || n_x > n_x_max) { e->err = "table entry counters are inconsistent"; return WC_ERR_CUDA; }
 
-    // Entries keep the record index space of the device order (word i -> i, long j -> n_w_max + j);
-    // slots without a record, and words whose count went back to zero, stay as count-0 entries.
+    if (device_reduce) {
+        // the rows are final: record index and count per row, in output order
+        const u64 n_valid = ((const u64 *)hfin)[3], n_rows = ((const u64 *)hfin)[4];
+        const wc::WordRecord *wr = (const wc::WordRecord *)(hfin + off_w);
+        const wc::LongRecord *xr = (const wc::LongRecord *)(hfin + off_x);
+        const u32 *row_idx = (const u32 *)(hfin + off_ri);
+        const u64 *row_cnt = (const u64 *)(hfin + off_rc);
+        wc_result *r = new (std::nothrow) wc_result();
+        if (!r) return WC_ERR_NOMEM;
+        r->rows.resize((size_t)n_rows);
+        size_t blob_bytes = 0;
+        for (u64 i = 0; i < n_rows; i++) {
+            const u32 idx = row_idx[i];
+            u32 len;
+            if (idx < n_w_max) {
+                const u64 k0 = wr[idx].k0, k1 = wr[idx].k1;
+                len = k1 ? 16 - (u32)(__builtin_clzll(k1) >> 3) : 8 - (u32)(__builtin_clzll(k0) >> 3);
+            } else len = (u32)xr[idx - n_w_max].len;
+            r->rows[i] = wc::Row{blob_bytes, len, (int64_t)row_cnt[i], idx < n_w_max ? wr[idx].first : xr[idx - n_w_max].first};
+            blob_bytes += len;
+        }
+        r->blob.resize(blob_bytes);
+        char *bp = &r->blob[0];
+        for (u64 i = 0; i < n_rows; i++) {
+            const u32 idx = row_idx[i];
+            const char *src = idx < n_w_max ? (const char *)&wr[idx] : (const char *)(hfin + off_b + xr[idx - n_w_max].blob_off);
+            memcpy(bp + r->rows[i].blob_off, src, r->rows[i].len);
+        }
+        const double t_decode = since();
+        const u64 total_bytes = e->job_stats_set ? e->job_bytes : e->consumed;
+        const u64 stop_abs = st.stop == wc::kNone ? e->cfg.base_offset + total_bytes : st.stop;
+        u64 lost = st.lost_empty;
+        if (!st.p0_found || st.p0 >= stop_abs) lost = st.n_empty; // no non-empty word at all: every empty one is lost
+        if (e->cfg.mode != WC_MODE_EXACT && n_rows) r->rows[0].count += (int64_t)(st.n_empty - lost); // main.cu:81-86
+        r->total = 0;
+        for (const wc::Row &row : r->rows) r->total += row.count;
+        r->stats.bytes = total_bytes;
+        r->stats.n_flush = st.n_flush; r->stats.n_empty = st.n_empty; r->stats.n_lost_empty = lost;
+        r->stats.stop = stop_abs - e->cfg.base_offset;
+        r->stats.n_distinct = n_valid;
+        r->stats.n_long_words = st.n_long; r->stats.n_spilled = st.n_spill; r->stats.n_slow_tiles = st.n_slow_tiles;
+        r->stats.table_grows = e->grows; r->stats.device_ms = e->device_ms; r->stats.count_kernel_ms = e->count_kernel_ms;
+        if (timing)
+            fprintf(stderr, "[wc] wc_finish: drain %.2f settle %.2f export+order+reduce+copy %.2f rows %.2f ms (%llu rows of %llu words)\n",
+                    t_sync, t_settle - t_sync, t_d2h - t_settle, t_decode - t_d2h, (unsigned long long)n_rows,
+                    (unsigned long long)n_valid);
+        *out = r;
+        return WC_OK;
+    }
+
+    // Host reduce (sort path, a single entry, or WC_HOST_REDUCE=1).  Entries keep the record index space
+    // of the device order (word i -> i, long j -> n_w_max + j); slots without a record, and words whose
+    // count went back to zero, stay as count-0 entries.
     const bool have_order = n_ord > 1;
     std::string blob;
     std::vector<wc::HostEntry> entries;
