@@ -77,6 +77,8 @@ struct wc_engine {
     size_t d_ord_cap = 0;
     void *d_fz = nullptr;                    // wc_finish: arrays of the device reduce (wc_reduce.cuh)
     size_t d_fz_cap = 0;
+    void *d_out = nullptr, *h_out = nullptr; // wc_finish: the finished rows and their words (device / pinned host)
+    size_t d_out_cap = 0, h_out_cap = 0;
     bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
     u64 job_bytes = 0;
 
@@ -189,6 +191,8 @@ void wc_destroy(wc_engine *e) {
     if (e->d_fin) cudaFree(e->d_fin);
     if (e->d_ord) cudaFree(e->d_ord);
     if (e->d_fz) cudaFree(e->d_fz);
+    if (e->d_out) cudaFree(e->d_out);
+    if (e->h_out) cudaFreeHost(e->h_out);
     if (e->h_fin) cudaFreeHost(e->h_fin);
     if (e->so_key) { cudaFree(e->so_key); cudaFree(e->so_count); cudaFree(e->so_first); }
     if (e->em.cursor) cudaFree(e->em.cursor);
@@ -687,7 +691,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
     // [cursors][word records][long records][blob][row record indices][row counts] go to the host;
     // [by_key][by_first] only when the host does the reduce (WC_HOST_REDUCE=1, a cross-check)
     static const bool host_reduce = getenv("WC_HOST_REDUCE") != nullptr;
-    const size_t copy_bytes = host_reduce ? need : off_pk;
+    const size_t copy_bytes = n_ord > 1 ? need : off_pk; // (host reduce with device orders: the two orders come along)
     rc = ensure_cursors(e);
     if (rc != WC_OK) return rc;
     if (need > e->d_fin_cap) {
@@ -696,7 +700,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
         CK(cudaMalloc(&e->d_fin, need + need / 4));
         e->d_fin_cap = need + need / 4;
     }
-    if (need > e->h_fin_cap) {
+    if (need > e->h_fin_cap && (host_reduce || n_ord <= 1)) { // (the device reduce has its own, smaller, host block)
         if (e->h_fin) cudaFreeHost(e->h_fin);
         e->h_fin = nullptr; e->h_fin_cap = 0;
         CK(cudaMallocHost(&e->h_fin, need + need / 4));
@@ -752,9 +756,11 @@ int wc_finish(wc_engine *e, wc_result **out) {
             // ---- the reduce itself (wc_reduce.cuh): owners by range-minimum queries in key order, counts
             // to the owners, rows compacted in order of first occurrence
             const size_t n1 = (n_ord + wc::kRmqBlock - 1) / wc::kRmqBlock, n2 = (n1 + wc::kRmqBlock - 1) / wc::kRmqBlock;
-            size_t tb_sel = 0;
+            size_t tb_sel = 0, tb_scan = 0;
             CK(cub::DeviceSelect::Flagged(nullptr, tb_sel, (const u32 *)nullptr, (const unsigned char *)nullptr, (u32 *)nullptr,
                                           (u64 *)nullptr, n, e->stream));
+            CK(cub::DeviceScan::ExclusiveSum(nullptr, tb_scan, (const u64 *)nullptr, (u64 *)nullptr, n, e->stream));
+            if (tb_scan > tb_sel) tb_sel = tb_scan;
             const size_t b1 = align_up(n1 * sizeof(u64), 256), b2 = align_up(n2 * sizeof(u64), 256);
             const size_t need_fz = 3 * a8 + 3 * a4 + align_up(n_ord, 256) + 2 * b1 + 2 * b2 + align_up(tb_sel, 256) + 256;
             if (need_fz > e->d_fz_cap) {
@@ -779,7 +785,16 @@ int wc_finish(wc_engine *e, wc_result **out) {
             A.bmin1 = (u64 *)zz; A.bpos1 = (u32 *)(zz + b1); A.bmin2 = (u64 *)(zz + 2 * b1); A.bpos2 = (u32 *)(zz + 2 * b1 + b2);
             void *sel_temp = zz + 2 * b1 + 2 * b2;
             A.counters = (u64 *)(zz + 2 * b1 + 2 * b2 + align_up(tb_sel, 256));
-            CK(cudaMemsetAsync(A.counters, 0, 2 * sizeof(u64), e->stream));
+            CK(cudaMemsetAsync(A.counters, 0, 4 * sizeof(u64), e->stream));
+            // the output block: [64-byte head][rows, room for n_ord][the rows' words, packed]
+            const size_t out_rows = 64, out_blob = out_rows + n_ord * sizeof(wc::RowOut), out_need = out_blob + n_w_max * 16 + blob_max;
+            if (out_need > e->d_out_cap) {
+                if (e->d_out) cudaFree(e->d_out);
+                e->d_out = nullptr; e->d_out_cap = 0;
+                CK(cudaMalloc(&e->d_out, out_need + out_need / 4));
+                e->d_out_cap = out_need + out_need / 4;
+            }
+            uint8_t *dout = (uint8_t *)e->d_out;
             const int gb = e->num_sms * 8;
             wc::reduce_gather_kernel<<<gb, 256, 0, e->stream>>>(A, lo);
             wc::reduce_blockmin_kernel<<<(unsigned)(n1 < 65535 ? n1 : 65535), wc::kRmqBlock, 0, e->stream>>>(A.s_first, nullptr, n_ord, A.bmin1, A.bpos1);
@@ -789,11 +804,16 @@ int wc_finish(wc_engine *e, wc_result **out) {
             size_t tbs = tb_sel;
             CK(cub::DeviceSelect::Flagged(sel_temp, tbs, A.by_first, (const unsigned char *)flags, (u32 *)(dfin + off_ri),
                                           A.counters + 1, n, e->stream));
-            wc::reduce_rowcounts_kernel<<<gb, 256, 0, e->stream>>>(A, (const u32 *)(dfin + off_ri), A.counters + 1,
-                                                                   (u64 *)(dfin + off_rc));
+            // the rows as the host wants them: word lengths -> prefix sum -> rows + packed words
+            u64 *lens = A.s_count, *offs = (u64 *)(dfin + off_rc); // (s_count is not needed any more; off_rc: n_ord u64)
+            wc::reduce_rowlens_kernel<<<gb, 256, 0, e->stream>>>(A, (const u32 *)(dfin + off_ri), A.counters + 1, lens);
+            tbs = tb_sel;
+            CK(cub::DeviceScan::ExclusiveSum(sel_temp, tbs, (const u64 *)lens, offs, n, e->stream));
+            wc::reduce_emit_rows_kernel<<<gb, 256, 0, e->stream>>>(A, (const u32 *)(dfin + off_ri), A.counters + 1, offs,
+                                                                   (wc::RowOut *)(dout + out_rows), dout + out_blob);
             CK(cudaGetLastError());
-            CK(cudaMemcpyAsync(dfin + 24, A.counters, 2 * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
-            e->launches += 7;
+            CK(cudaMemcpyAsync(dout, A.counters, 4 * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
+            e->launches += 9;
         }
     }
     // cursors into the head of the block: [0] word records, [1] long records, [2] blob bytes
@@ -801,62 +821,44 @@ int wc_finish(wc_engine *e, wc_result **out) {
     CK(cudaMemcpyAsync(dfin + 8, e->d_cursors + 2 * kMaxParts, 2 * sizeof(u64), cudaMemcpyDeviceToDevice, e->stream));
     const bool device_reduce = n_ord > 1 && !host_reduce;
     if (device_reduce) {
-        // rows are usually far fewer than entries: fetch the head first, then exactly the rows
-        CK(cudaMemcpyAsync(hfin, dfin, off_ri, cudaMemcpyDeviceToHost, e->stream));
+        static_assert(sizeof(wc::RowOut) == sizeof(wc::Row) && offsetof(wc::Row, len) == 8 && offsetof(wc::Row, count) == 16 &&
+                          offsetof(wc::Row, first) == 24, "RowOut must mirror wc::Row");
+        const size_t out_rows = 64, out_blob = out_rows + n_ord * sizeof(wc::RowOut), out_need = out_blob + n_w_max * 16 + blob_max;
+        if (out_need > e->h_out_cap) {
+            if (e->h_out) cudaFreeHost(e->h_out);
+            e->h_out = nullptr; e->h_out_cap = 0;
+            CK(cudaMallocHost(&e->h_out, out_need + out_need / 4));
+            e->h_out_cap = out_need + out_need / 4;
+        }
+        uint8_t *dout = (uint8_t *)e->d_out, *hout = (uint8_t *)e->h_out;
+        // the head first (how many rows, how many bytes of words), then exactly those
+        CK(cudaMemcpyAsync(hout, dout, 64, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
-        const u64 n_rows = ((const u64 *)hfin)[4];
-        if (n_rows > n_ord) { e->err = "row counter is inconsistent"; return WC_ERR_CUDA; }
+        const u64 n_valid = ((const u64 *)hout)[0], n_rows = ((const u64 *)hout)[1], sum_counts = ((const u64 *)hout)[2],
+                  words_bytes = n_rows ? ((const u64 *)hout)[3] : 0;
+        if (n_rows > n_ord || words_bytes > n_w_max * 16 + blob_max) { e->err = "row counters are inconsistent"; return WC_ERR_CUDA; }
         if (n_rows) {
-            CK(cudaMemcpyAsync(hfin + off_ri, dfin + off_ri, n_rows * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
-            CK(cudaMemcpyAsync(hfin + off_rc, dfin + off_rc, n_rows * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaMemcpyAsync(hout + out_rows, dout + out_rows, n_rows * sizeof(wc::RowOut), cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaMemcpyAsync(hout + out_blob, dout + out_blob, words_bytes, cudaMemcpyDeviceToHost, e->stream));
             CK(cudaStreamSynchronize(e->stream));
         }
-        e->finish_d2h = off_ri + n_rows * 12 + sizeof(wc::Status);
-    } else {
-        CK(cudaMemcpyAsync(hfin, dfin, copy_bytes, cudaMemcpyDeviceToHost, e->stream));
-        CK(cudaStreamSynchronize(e->stream));
-        e->finish_d2h = copy_bytes + sizeof(wc::Status);
-    }
-    const double t_d2h = since();
-    const u64 n_w = ((const u64 *)hfin)[0], n_x = ((const u64 *)hfin)[1];
-    if (n_w > n_w_max || n_x > n_x_max) { e->err = "table entry counters are inconsistent"; return WC_ERR_CUDA; }
-
-    if (device_reduce) {
-        // the rows are final: record index and count per row, in output order
-        const u64 n_valid = ((const u64 *)hfin)[3], n_rows = ((const u64 *)hfin)[4];
-        const wc::WordRecord *wr = (const wc::WordRecord *)(hfin + off_w);
-        const wc::LongRecord *xr = (const wc::LongRecord *)(hfin + off_x);
-        const u32 *row_idx = (const u32 *)(hfin + off_ri);
-        const u64 *row_cnt = (const u64 *)(hfin + off_rc);
+        e->finish_d2h = 64 + n_rows * sizeof(wc::RowOut) + words_bytes + sizeof(wc::Status);
+        const double t_d2h = since();
         wc_result *r = new (std::nothrow) wc_result();
         if (!r) return WC_ERR_NOMEM;
-        r->rows.resize((size_t)n_rows);
-        size_t blob_bytes = 0;
-        for (u64 i = 0; i < n_rows; i++) {
-            const u32 idx = row_idx[i];
-            u32 len;
-            if (idx < n_w_max) {
-                const u64 k0 = wr[idx].k0, k1 = wr[idx].k1;
-                len = k1 ? 16 - (u32)(__builtin_clzll(k1) >> 3) : 8 - (u32)(__builtin_clzll(k0) >> 3);
-            } else len = (u32)xr[idx - n_w_max].len;
-            r->rows[i] = wc::Row{blob_bytes, len, (int64_t)row_cnt[i], idx < n_w_max ? wr[idx].first : xr[idx - n_w_max].first};
-            blob_bytes += len;
-        }
-        r->blob.resize(blob_bytes);
-        char *bp = &r->blob[0];
-        for (u64 i = 0; i < n_rows; i++) {
-            const u32 idx = row_idx[i];
-            const char *src = idx < n_w_max ? (const char *)&wr[idx] : (const char *)(hfin + off_b + xr[idx - n_w_max].blob_off);
-            memcpy(bp + r->rows[i].blob_off, src, r->rows[i].len);
-        }
+        const wc::Row *rp = (const wc::Row *)(hout + out_rows);
+        r->rows.assign(rp, rp + n_rows);
+        r->blob.assign((const char *)(hout + out_blob), (size_t)words_bytes);
         const double t_decode = since();
         const u64 total_bytes = e->job_stats_set ? e->job_bytes : e->consumed;
         const u64 stop_abs = st.stop == wc::kNone ? e->cfg.base_offset + total_bytes : st.stop;
         u64 lost = st.lost_empty;
         if (!st.p0_found || st.p0 >= stop_abs) lost = st.n_empty; // no non-empty word at all: every empty one is lost
-        if (e->cfg.mode != WC_MODE_EXACT && n_rows) r->rows[0].count += (int64_t)(st.n_empty - lost); // main.cu:81-86
-        r->total = 0;
-        for (const wc::Row &row : r->rows) r->total += row.count;
+        r->total = (int64_t)sum_counts; // every word is credited to exactly one row
+        if (e->cfg.mode != WC_MODE_EXACT && n_rows) { // empty words after the first real one go to row 0 (main.cu:81-86)
+            r->rows[0].count += (int64_t)(st.n_empty - lost);
+            r->total += (int64_t)(st.n_empty - lost);
+        }
         r->stats.bytes = total_bytes;
         r->stats.n_flush = st.n_flush; r->stats.n_empty = st.n_empty; r->stats.n_lost_empty = lost;
         r->stats.stop = stop_abs - e->cfg.base_offset;
@@ -870,6 +872,12 @@ int wc_finish(wc_engine *e, wc_result **out) {
         *out = r;
         return WC_OK;
     }
+    CK(cudaMemcpyAsync(hfin, dfin, copy_bytes, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->finish_d2h = copy_bytes + sizeof(wc::Status);
+    const double t_d2h = since();
+    const u64 n_w = ((const u64 *)hfin)[0], n_x = ((const u64 *)hfin)[1];
+    if (n_w > n_w_max || n_x > n_x_max) { e->err = "table entry counters are inconsistent"; return WC_ERR_CUDA; }
 
     // Host reduce (sort path, a single entry, or WC_HOST_REDUCE=1).  Entries keep the record index space
     // of the device order (word i -> i, long j -> n_w_max + j); slots without a record, and words whose

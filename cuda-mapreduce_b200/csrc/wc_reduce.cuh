@@ -38,12 +38,13 @@ struct ReduceArrays {
     u32 *owner;                     // s -> s of its owner
     u64 *acc;                       // s -> sum of the counts it owns
     u64 *bmin1; u32 *bpos1; u64 *bmin2; u32 *bpos2;
-    u64 *counters;                  // [0] valid entries, [1] rows
+    u64 *counters;                  // [0] valid entries, [1] rows, [2] sum of all counts, [3] bytes of the rows' words
 };
 
 __global__ void reduce_gather_kernel(ReduceArrays A, const u64 *lo_by_idx) {
     const u64 n_w = *A.n_w_ptr, n_x = *A.n_x_ptr;
     u32 valid = 0;
+    u64 words = 0;
     for (u64 s = blockIdx.x * (u64)blockDim.x + threadIdx.x; s < A.n; s += (u64)gridDim.x * blockDim.x) {
         const u32 idx = A.by_key[s];
         A.pos_of_idx[idx] = (u32)s;
@@ -61,10 +62,12 @@ __global__ void reduce_gather_kernel(ReduceArrays A, const u64 *lo_by_idx) {
         }
         if (cnt == 0 || len == 0) { len = 0; first = ~0ull; cnt = 0; } // a slot without a record, or a rolled-back word
         valid += len != 0;
+        words += cnt;
         A.s_len[s] = len; A.s_first[s] = first; A.s_count[s] = cnt; A.acc[s] = 0;
     }
     valid = __reduce_add_sync(0xFFFFFFFFu, valid);
-    if ((threadIdx.x & 31) == 0 && valid) atomicAdd(&A.counters[0], (u64)valid);
+    words = warp_sum64(words);
+    if ((threadIdx.x & 31) == 0 && valid) { atomicAdd(&A.counters[0], (u64)valid); atomicAdd(&A.counters[2], words); }
 }
 
 // One block per kRmqBlock inputs: min value and where it is.  pos_in == nullptr: positions are the indices.
@@ -182,10 +185,35 @@ __global__ void reduce_rowflags_kernel(ReduceArrays A, unsigned char *flags) {
     }
 }
 
-__global__ void reduce_rowcounts_kernel(ReduceArrays A, const u32 *row_idx, const u64 *n_rows_ptr, u64 *row_cnt) {
+// The result as the host wants it (layout of wc::Row in wc_finalize.h): rows in output order, their words packed
+// back to back.  lens[r] feeds the prefix sum that places the words.
+struct RowOut { u64 blob_off; u32 len; u32 pad; u64 count; u64 first; };
+
+__global__ void reduce_rowlens_kernel(ReduceArrays A, const u32 *row_idx, const u64 *n_rows_ptr, u64 *lens) {
     const u64 n_rows = *n_rows_ptr;
-    for (u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x; r < n_rows; r += (u64)gridDim.x * blockDim.x)
-        row_cnt[r] = A.acc[A.pos_of_idx[row_idx[r]]];
+    for (u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x; r < A.n; r += (u64)gridDim.x * blockDim.x)
+        lens[r] = r < n_rows ? A.s_len[A.pos_of_idx[row_idx[r]]] : 0;
+}
+
+__global__ void reduce_emit_rows_kernel(ReduceArrays A, const u32 *row_idx, const u64 *n_rows_ptr, const u64 *offs, RowOut *rows,
+                                        uint8_t *blob_out) {
+    const u64 n_rows = *n_rows_ptr;
+    for (u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x; r < n_rows; r += (u64)gridDim.x * blockDim.x) {
+        const u32 idx = row_idx[r];
+        const u32 s = A.pos_of_idx[idx];
+        const u32 len = A.s_len[s];
+        const u64 off = offs[r];
+        rows[r] = RowOut{off, len, 0u, A.acc[s], A.s_first[s]};
+        uint8_t *dst = blob_out + off;
+        if (idx < A.n_w_max) {
+            const WordRecord w = A.w[idx];
+            for (u32 b = 0; b < len; b++) dst[b] = (uint8_t)((b < 8 ? w.k0 >> (8 * b) : w.k1 >> (8 * (b - 8))) & 0xFF);
+        } else {
+            const uint8_t *src = reinterpret_cast<const uint8_t *>(A.blob) + A.x[idx - A.n_w_max].blob_off;
+            for (u32 b = 0; b < len; b++) dst[b] = src[b];
+        }
+        if (r == n_rows - 1) A.counters[3] = off + len;
+    }
 }
 
 } // namespace wc
