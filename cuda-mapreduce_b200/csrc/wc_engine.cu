@@ -847,8 +847,22 @@ int wc_finish(wc_engine *e, wc_result **out) {
         wc_result *r = new (std::nothrow) wc_result();
         if (!r) return WC_ERR_NOMEM;
         const wc::Row *rp = (const wc::Row *)(hout + out_rows);
-        r->rows.assign(rp, rp + n_rows);
-        r->blob.assign((const char *)(hout + out_blob), (size_t)words_bytes);
+        wc::Row *row0 = nullptr;
+        const char *big_env = getenv("WC_BIG_RESULT_BYTES"); // (tests lower the threshold to reach this path)
+        const size_t big_at = big_env ? (size_t)strtoull(big_env, nullptr, 10) : ((size_t)256 << 20);
+        if (n_rows * sizeof(wc::Row) + words_bytes >= big_at) { // large: uninitialised arrays, filled by several threads
+            r->big_rows = (wc::Row *)malloc(n_rows * sizeof(wc::Row));
+            r->big_blob = (char *)malloc(words_bytes ? words_bytes : 1);
+            if (!r->big_rows || !r->big_blob) { delete r; return WC_ERR_NOMEM; }
+            r->n_big_rows = n_rows;
+            wc::parallel_copy(r->big_rows, rp, n_rows * sizeof(wc::Row));
+            wc::parallel_copy(r->big_blob, hout + out_blob, words_bytes);
+            row0 = r->big_rows;
+        } else {
+            r->rows.assign(rp, rp + n_rows);
+            r->blob.assign((const char *)(hout + out_blob), (size_t)words_bytes);
+            row0 = r->rows.data();
+        }
         const double t_decode = since();
         const u64 total_bytes = e->job_stats_set ? e->job_bytes : e->consumed;
         const u64 stop_abs = st.stop == wc::kNone ? e->cfg.base_offset + total_bytes : st.stop;
@@ -856,7 +870,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
         if (!st.p0_found || st.p0 >= stop_abs) lost = st.n_empty; // no non-empty word at all: every empty one is lost
         r->total = (int64_t)sum_counts; // every word is credited to exactly one row
         if (e->cfg.mode != WC_MODE_EXACT && n_rows) { // empty words after the first real one go to row 0 (main.cu:81-86)
-            r->rows[0].count += (int64_t)(st.n_empty - lost);
+            row0[0].count += (int64_t)(st.n_empty - lost);
             r->total += (int64_t)(st.n_empty - lost);
         }
         r->stats.bytes = total_bytes;

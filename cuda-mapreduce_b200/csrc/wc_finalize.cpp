@@ -5,10 +5,30 @@
 #include <cstdio>
 #include <cstring>
 #include <numeric>
+#include <thread>
 #include <chrono>
 #include <cstdlib>
 
+wc_result::~wc_result() { free(big_rows); free(big_blob); }
+
 namespace wc {
+
+void parallel_copy(void *dst, const void *src, size_t bytes) {
+    const size_t kMin = (size_t)32 << 20;
+    unsigned hw = std::thread::hardware_concurrency();
+    size_t nt = bytes / kMin;
+    if (nt > 8) nt = 8;
+    if (hw && nt > hw) nt = hw;
+    if (nt < 2) { memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> th;
+    const size_t step = ((bytes / nt) + 4095) & ~(size_t)4095;
+    for (size_t t = 0; t < nt; t++) {
+        const size_t lo = t * step, hi = (t + 1 == nt || (t + 1) * step > bytes) ? bytes : (t + 1) * step;
+        if (lo >= hi) break;
+        th.emplace_back([=] { memcpy((char *)dst + lo, (const char *)src + lo, hi - lo); });
+    }
+    for (auto &x : th) x.join();
+}
 
 // The reference's reducer (main.cu:69-108) walks the words in input order and credits each one to
 // the FIRST output row of which it is a prefix (compare(), main.cu:57-67), appending a row when
@@ -158,18 +178,19 @@ void finalize_rows(std::string &&blob_in, std::vector<HostEntry> &v, int mode, u
 
 extern "C" {
 
-size_t wc_result_rows(const wc_result *r) { return r ? r->rows.size() : 0; }
+size_t wc_result_rows(const wc_result *r) { return r ? r->row_count() : 0; }
 
 int wc_result_row(const wc_result *r, size_t i, const char **word, size_t *len, int64_t *count) {
-    if (!r || i >= r->rows.size()) return WC_ERR_INVALID;
-    if (word) *word = r->blob.data() + r->rows[i].blob_off;
-    if (len) *len = r->rows[i].len;
-    if (count) *count = r->rows[i].count;
+    if (!r || i >= r->row_count()) return WC_ERR_INVALID;
+    const wc::Row &row = r->row_data()[i];
+    if (word) *word = r->blob_data() + row.blob_off;
+    if (len) *len = row.len;
+    if (count) *count = row.count;
     return WC_OK;
 }
 
 uint64_t wc_result_row_first(const wc_result *r, size_t i) {
-    return (!r || i >= r->rows.size()) ? ~0ull : r->rows[i].first;
+    return (!r || i >= r->row_count()) ? ~0ull : r->row_data()[i].first;
 }
 
 int64_t wc_result_total(const wc_result *r) { return r ? r->total : 0; }
@@ -193,8 +214,9 @@ size_t wc_result_render(const wc_result *r, char *buf, size_t cap) {
     char num[48];
     put(sep, sizeof(sep) - 1);
     if (r)
-        for (const wc::Row &row : r->rows) {
-            put(r->blob.data() + row.blob_off, row.len);
+        for (size_t i = 0; i < r->row_count(); i++) {
+            const wc::Row &row = r->row_data()[i];
+            put(r->blob_data() + row.blob_off, row.len);
             int k = snprintf(num, sizeof(num), "\t%lld\n", (long long)row.count);
             put(num, (size_t)k);
         }

@@ -29,8 +29,18 @@ struct Row {
 struct wc_result {
     std::string blob; // bytes of every row's word
     std::vector<wc::Row> rows;
+    // Large results (wc_finish with 10^8 rows) are copied into plain malloc'd arrays by several
+    // threads instead: a vector would first zero-fill every page on one core.
+    wc::Row *big_rows = nullptr; size_t n_big_rows = 0; char *big_blob = nullptr;
     int64_t total = 0;
     wc_stats stats{};
+    const wc::Row *row_data() const { return big_rows ? big_rows : rows.data(); }
+    size_t row_count() const { return big_rows ? n_big_rows : rows.size(); }
+    const char *blob_data() const { return big_blob ? big_blob : blob.data(); }
+    ~wc_result();
+    wc_result() = default;
+    wc_result(const wc_result &) = delete;
+    wc_result &operator=(const wc_result &) = delete;
 };
 
 namespace wc {
@@ -40,6 +50,9 @@ namespace wc {
 // Optional, both or neither (wc_finish computes them on the GPU): `by_key` lists entry indices
 // ordered by the words' first 16 bytes (bytewise, shorter first; ties between longer words in any
 // order), `by_first` ordered by `first`; entries with count 0 are placeholders and are skipped.
+// dst <- src with several threads when it is worth it (large, freshly allocated destinations)
+void parallel_copy(void *dst, const void *src, size_t bytes);
+
 void finalize_rows(std::string &&blob, std::vector<HostEntry> &entries, int mode, uint64_t n_empty,
                    uint64_t n_lost_empty, wc_result *out, const uint32_t *by_key = nullptr,
                    const uint32_t *by_first = nullptr);

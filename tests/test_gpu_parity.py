@@ -406,6 +406,17 @@ def test_peer_gather_three_engines_one_gpu(pkg):
             e.close()
 
 
+def test_large_result_storage(pkg, monkeypatch):
+    """Results of hundreds of MB leave wc_finish in plain arrays filled by several threads; the
+    threshold is lowered here so that an ordinary text takes that path."""
+    rng = random.Random(33)
+    data = random_text(rng, 60000, weird=0.01)
+    monkeypatch.setenv("WC_BIG_RESULT_BYTES", "1")
+    with pkg.Engine(chunk_bytes=1 << 20, **SMALL) as e:
+        check_against_oracle(e, data)
+        check_against_oracle(e, data[:1000])
+
+
 def test_word_table_grows_instead_of_overflowing(pkg):
     """A word table far too small for the vocabulary: words it cannot take go to the overflow log, the
     host re-hashes into a larger table and replays the log -- nothing is lost (wc_engine.cu
