@@ -327,7 +327,7 @@ def main():
                    "l2": "input (1e9 B) is larger than the 126 MB L2, every step re-reads it from HBM",
                    "step": "wc_reset (table memset) + tokenize/count kernel + roll-back/summary kernel"
                            + ((" + gather on rank 0 through NVLink peer memory (one push kernel per sender, one-word NCCL all-reduce as barrier)"
-                              if gather else " + key-owner exchange (NCCL all-to-all, owner reduce, gather on rank 0)") if world > 1 else ""),
+                              if (gather and gather.available) else " + key-owner exchange (NCCL all-to-all, owner reduce, gather on rank 0)") if world > 1 else ""),
                    "vocab_seed": corpus.vocab_seed, "text_seed": corpus.text_seed},
         "words_per_s": all_words / (ms_step * 1e-3),
         "frac_of_hbm_nominal_8TBs": value / world / 8000.0,

@@ -194,19 +194,30 @@ class PeerGather:
         world, rank = dist.get_world_size(), dist.get_rank()
         caps = (words_per_rank, long_per_rank, blob_bytes_per_rank)
         handle = torch.zeros(64, dtype=torch.uint8, device=device)
-        if rank == root:
-            raw = engine.peer_root_create(world, root, *caps)
-            handle.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+        ok = torch.ones(1, dtype=torch.int32, device=device)
+        self.why = ""
+        try:
+            if rank == root:
+                raw = engine.peer_root_create(world, root, *caps)
+                handle.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+        except wc.WcError as ex:
+            ok.zero_(); self.why = str(ex)
         dist.broadcast(handle, src=root)
-        if rank != root:
-            engine.peer_open(rank, world, root, *caps, bytes(handle.cpu().numpy().tobytes()))
+        try:
+            if rank != root:
+                engine.peer_open(rank, world, root, *caps, bytes(handle.cpu().numpy().tobytes()))
+        except wc.WcError as ex:  # no CUDA IPC / no peer access on this machine
+            ok.zero_(); self.why = str(ex)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        self.available = int(ok.item()) == 1  # False on every rank if it failed on any: use exchange_and_gather
         self.flag = torch.zeros(1, dtype=torch.int32, device=device)
-        dist.barrier()
 
     def run(self):
         """Call on the engine's stream (torch.cuda.stream(ExternalStream(engine.stream()))).
         Returns (job_stats or None, is_root)."""
         rank = dist.get_rank()
+        if not self.available:
+            return exchange_and_gather(self.engine, self.device, self.root)
         self.flag.zero_()
         if rank != self.root:
             self.engine.peer_push(self.flag.data_ptr())
