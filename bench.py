@@ -173,6 +173,8 @@ def main():
     ap.add_argument("--table-log2", type=int, default=0, help="override the word table size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    ap.add_argument("--strict-ref", action="store_true",
+                    help="WC_FLAG_STRICT_REF: read lines in 99-byte pieces like the reference's fgets (same results on these corpora)")
     ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
                     help="N > 1: gather through NVLink peer memory (default) or the NCCL all-to-all protocol")
     args = ap.parse_args()
@@ -215,7 +217,7 @@ def main():
     dev = host.cuda(non_blocking=False)
 
     eng = pkg.Engine(device=local_rank, short_table_log2=wp["s_log2"], long_table_log2=wp["l_log2"], base_offset=lo,
-                     path={"auto": 0, "hash": 1, "sort": 2}[args.path])
+                     path={"auto": 0, "hash": 1, "sort": 2}[args.path], strict_ref=args.strict_ref)
     ext = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local_rank))
     # N > 1: table entries go to rank 0 through NVLink peer memory (wc_peer_*), one kernel per sender and
     # a one-word all-reduce as the barrier; --exchange nccl uses the all-to-all protocol instead.

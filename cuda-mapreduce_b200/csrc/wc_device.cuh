@@ -118,6 +118,7 @@ struct Launch {
     u32 tiles_per_warp;
     int last_piece;     // the input ends with this piece
     int negate;         // roll-back launch: subtract everything at or after Status::stop
+    int strict;         // read lines in pieces of kLineCap bytes like the reference's fgets does (main.cu:175,179)
     WarpSummary *ws;
     u32 n_ws;
     EmitBuf em;
@@ -450,13 +451,14 @@ struct WarpCarry {
     long long last_delim; // buffer-relative position of the last delimiter byte seen, -1 if none
     bool killed;          // a 0x0D / 0x00 since the last 0x0A: rest of the line is not split (main.cu:187,196)
     bool last_is_lf;      // previous byte was 0x0A (or this is the start of the piece)
+    long long line_start; // buffer-relative position of the first byte of the line that holds pos
 };
 
 // State at buffer offset `pos` (> 0), found by scanning backwards to the previous line start.
 __device__ __forceinline__ WarpCarry warp_lookback(const uint8_t *buf, u64 pos) {
     const u32 lane = lane_id();
     WarpCarry c;
-    c.last_delim = -1; c.killed = false;
+    c.last_delim = -1; c.killed = false; c.line_start = 0;
     c.last_is_lf = buf[pos - 1] == 0x0A;
     bool have_delim = false, seen_kill = false;
     for (long long hi = (long long)pos; hi > 0; hi -= 32) { // window [hi-32, hi), lane 0 nearest
@@ -469,6 +471,7 @@ __device__ __forceinline__ WarpCarry warp_lookback(const uint8_t *buf, u64 pos) 
         if (bl) { // nearest line feed: kills between it and pos count
             u32 nearer = (1u << (__ffs(bl) - 1)) - 1;
             c.killed = seen_kill || (bk & nearer);
+            c.line_start = hi - (long long)(__ffs(bl) - 1); // the byte after that line feed
             return c;
         }
         seen_kill = seen_kill || bk;
@@ -557,6 +560,70 @@ __device__ __noinline__ ExactOut exact_sub(uint4 v, u32 killed_in, const uint8_t
             if (at0) atomicMin(stop_ptr, base + i);
             else if (at1) atomicMin(stop_ptr, base + i - 1);
         }
+    }
+    return o;
+}
+
+// ---- strict-ref mode: the reference reads with fgets(szLine, 100) (main.cu:175,179),
+// i.e. a line longer than 99 bytes arrives in PIECES of 99 bytes, and everything main.cu does per line
+// it really does per piece: the pending word is dropped at a piece's end (so a word that straddles the
+// edge loses its head), 0x0D / 0x00 hide only the rest of the piece, and a piece of one byte stops the
+// input (main.cu:185).  A "piece start" is a line start or a byte at line offset 99, 198, ...
+constexpr u32 kLineCap = 99;
+
+// Any 0x0D / 0x00 in buf[lo, hi)?  (hi - lo < 128; whole warp)
+__device__ __forceinline__ bool warp_any_kill(const uint8_t *buf, long long lo, long long hi) {
+    bool any = false;
+    for (long long p = lo + lane_id(); __any_sync(0xFFFFFFFFu, p < hi); p += 32) {
+        const u32 ch = p < hi ? buf[p] : 0x78u;
+        any = any || __any_sync(0xFFFFFFFFu, ch == 0x0D || ch == 0x00);
+    }
+    return any;
+}
+
+// Exact masks of one lane's 32 bytes when pieces matter.  starts: bit p = byte p starts a line or a piece;
+// carry_start: the byte before this lane's first byte starts one.
+struct StrictOut { u32 dm, live, lfm, killed_out; };
+__device__ __noinline__ StrictOut strict_exact(uint4 va, uint4 vb, u32 starts, u32 carry_start, u32 killed_in, u64 abs_pos,
+                                               u64 *stop_ptr, int negate) {
+    const u32 lane = lane_id();
+    StrictOut o;
+    u32 km;
+    {
+        const ByteFlags a0 = classify4(va.x), a1 = classify4(va.y), a2 = classify4(va.z), a3 = classify4(va.w);
+        const ByteFlags b0 = classify4(vb.x), b1 = classify4(vb.y), b2 = classify4(vb.z), b3 = classify4(vb.w);
+        o.dm = movemask16(a0.delim, a1.delim, a2.delim, a3.delim) | (movemask16(b0.delim, b1.delim, b2.delim, b3.delim) << 16);
+        o.lfm = movemask16(a0.lf, a1.lf, a2.lf, a3.lf) | (movemask16(b0.lf, b1.lf, b2.lf, b3.lf) << 16);
+        km = movemask16(a0.kill, a1.kill, a2.kill, a3.kill) | (movemask16(b0.kill, b1.kill, b2.kill, b3.kill) << 16);
+    }
+    // per-lane transfer function of "killed": s -> reset ? val : (s | val); a piece start resets it
+    u32 reset = starts != 0;
+    u32 val = reset ? ((km >> (31 - __clz(starts))) != 0) : (km != 0);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 r2 = __shfl_up_sync(0xFFFFFFFFu, reset, d);
+        const u32 v2 = __shfl_up_sync(0xFFFFFFFFu, val, d);
+        if (lane >= (u32)d) { val = reset ? val : (val | v2); reset = reset | r2; }
+    }
+    const u32 r_in = __shfl_up_sync(0xFFFFFFFFu, reset, 1), v_in = __shfl_up_sync(0xFFFFFFFFu, val, 1);
+    bool s = killed_in != 0;
+    if (lane > 0) s = r_in ? (v_in != 0) : (s || v_in);
+    const u32 r_all = __shfl_sync(0xFFFFFFFFu, reset, 31), v_all = __shfl_sync(0xFFFFFFFFu, val, 31);
+    o.killed_out = r_all ? (v_all != 0) : (killed_in || v_all);
+    o.live = 0;
+#pragma unroll 4
+    for (int p = 0; p < 32; p++) {
+        const u32 bit = 1u << p;
+        if (starts & bit) s = false;
+        if ((o.dm & bit) && !s) o.live |= bit;
+        if (km & bit) s = true;
+    }
+    // A NUL at offset 0 or 1 of a piece makes strlen() < 2: the reference stops at that piece (main.cu:185).
+    if (!negate) {
+        const u32 nm = km & ~o.dm;
+        const u32 at0 = nm & starts, at1 = nm & ((starts << 1) | (carry_start & 1u)) & ~starts;
+        if (at0) atomicMin(stop_ptr, abs_pos + (__ffs(at0) - 1));
+        if (at1) atomicMin(stop_ptr, abs_pos + (__ffs(at1) - 1) - 1);
     }
     return o;
 }
@@ -904,12 +971,22 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
         // carry from tile to tile: position of the last delimiter (relative to the NEXT tile's start,
         // so always negative), the line state, and whether the previous byte was a line feed
         int carry_prev; bool killed, last_is_lf;
+        u32 lmod = 0; // strict-ref: line offset of the tile's first byte, modulo the reference's line buffer
         if (t0 == 0) { carry_prev = -1; killed = false; last_is_lf = true; }
         else {
             const WarpCarry c = warp_lookback(L.buf, (u64)t0 * kTile);
             const long long cr = c.last_delim - (long long)t0 * kTile;
             carry_prev = cr < -(1ll << 30) ? -(1 << 30) : (int)cr;
             killed = c.killed; last_is_lf = c.last_is_lf;
+            if (L.strict) { // where in its line's 99-byte pieces does this range begin?
+                const long long pos = (long long)t0 * kTile;
+                lmod = (u32)((pos - c.line_start) % (long long)kLineCap);
+                const long long c0 = pos - (long long)lmod; // the last piece start at or before pos
+                if (c0 > c.line_start) { // it lies inside the line: the piece, not the line, bounds what came before
+                    killed = lmod ? warp_any_kill(L.buf, c0, pos) : false;
+                    if (c.last_delim < c0 - 1) carry_prev = -(int)lmod - 1;
+                }
+            }
             // the bytes just before the range, where a word ending in the first tile may start
             if (lane == 0)
                 *reinterpret_cast<uint4 *>(wbase + (t0 & 1) * kBufBytes) = load16(L.buf, L.n, (u64)t0 * kTile - 16);
@@ -932,6 +1009,10 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             const u64 T0 = (u64)t * kTile;          // buffer-relative offset of this tile
             const u32 relT = (u32)(T0 - cta_base);
 
+            // strict-ref: a piece start at the tile's first byte acts like a delimiter just before the tile
+            if (L.strict && lmod == 0 && !last_is_lf) carry_prev = -1;
+            u32 cs_mid = 0, lmod_next = 0; // strict-ref: this lane's piece start that is not a line start (one bit at most)
+
             // ---- classify 2 x 16 bytes
             u32 dm, lf, live;
             {
@@ -953,7 +1034,37 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     ex |= b0.ex | b1.ex | b2.ex | b3.ex;
                 }
                 live = dm;
-                if (__any_sync(0xFFFFFFFFu, ex != 0) || killed) {
+                if (L.strict) {
+                    // Line offset (mod 99) of this lane's first byte: from the nearest line feed in the
+                    // lanes before it, else from the carry.  A lane holds at most one piece start that is
+                    // not a line start: at p* = (99 - offset) mod 99, if that is before its first line feed.
+                    const int mylast = lf ? (int)(lane * 32 + 31 - __clz(lf)) : -1;
+                    int incl = mylast;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const int tv = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                        if (lane >= (u32)d && tv > incl) incl = tv;
+                    }
+                    int qprev = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
+                    if (lane == 0) qprev = -1;
+                    const u32 off_mod = qprev >= 0 ? (u32)((int)(lane * 32) - (qprev + 1)) % kLineCap : (lmod + lane * 32) % kLineCap;
+                    const bool line_start = qprev >= 0 ? (qprev + 1 == (int)(lane * 32)) : (lane == 0 && last_is_lf);
+                    const u32 pstar = off_mod == 0 ? 0u : kLineCap - off_mod;
+                    const u32 first_lf = lf ? (u32)__ffs(lf) - 1 : 32u;
+                    if (pstar < 32 && pstar <= first_lf && !(pstar == 0 && line_start)) cs_mid = 1u << pstar;
+                    const int last_lf_tile = __shfl_sync(0xFFFFFFFFu, incl, 31);
+                    lmod_next = last_lf_tile >= 0 ? (u32)(kTile - 1 - last_lf_tile) % kLineCap : (lmod + kTile) % kLineCap;
+                    if (__any_sync(0xFFFFFFFFu, ex != 0 || cs_mid != 0) || killed) {
+                        acc_slow += lane == 0;
+                        const u32 up_lf = __shfl_up_sync(0xFFFFFFFFu, lf >> 31, 1);
+                        const u32 starts = (lf << 1) | (lane == 0 ? (last_is_lf ? 1u : 0u) : up_lf) | cs_mid;
+                        const u32 up_st = __shfl_up_sync(0xFFFFFFFFu, starts >> 31, 1);
+                        const u32 carry_start = lane == 0 ? (lmod == 1 ? 1u : 0u) : up_st;
+                        const StrictOut so = strict_exact(va, vb, starts, carry_start, killed, L.base + T0 + lane * 32,
+                                                          &st->stop, L.negate);
+                        dm = so.dm; live = so.live; lf = so.lfm; killed = so.killed_out != 0;
+                    }
+                } else if (__any_sync(0xFFFFFFFFu, ex != 0) || killed) {
                     // The exact path sees the tile as two 512-byte halves of 16 bytes per lane; its masks
                     // are handed back to the lanes that own those bytes here.
                     acc_slow += lane == 0;
@@ -977,7 +1088,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             }
             // ---- STOP: a line that is just "\n" (main.cu:185), or a 1-byte tail at the very end
             if (!L.negate) {
-                const u32 start = (lf << 1) | (prev & 1u); // bit p: byte p starts a line
+                const u32 start = (lf << 1) | (prev & 1u) | cs_mid; // bit p: byte p starts a line (strict-ref: or a piece)
                 const u32 blank = lf & start;
                 if (blank) atomicMin(&st->stop, L.base + T0 + lane * 32 + (__ffs(blank) - 1));
                 if (t == last_tile && L.last_piece) {
@@ -994,7 +1105,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             }
 
             // ---- flush counts straight from the masks: a flush right after a delimiter is an empty word
-            const u32 after = (dm << 1) | (prev >> 1);
+            const u32 after = (dm << 1) | (prev >> 1) | cs_mid; // (strict-ref: a flush at a piece start is an empty word too)
             const u32 em = live & after;
             acc_flush += __popc(live);
             acc_empty += __popc(em);
@@ -1013,8 +1124,15 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                 my_empties_before += __reduce_add_sync(0xFFFFFFFFu, x);
             }
 
-            // ---- position-ordered list of every delimiter
-            const u32 cnt = __popc(dm);
+            // ---- position-ordered list of every delimiter.  strict-ref: a piece start at byte c that does
+            // not follow a delimiter adds an entry at c - 1 that never flushes: the word before it is
+            // dropped there and the next one starts at c (main.cu:183: nIndex = 0 for every fgets).
+            u32 lm = dm;
+            if (L.strict) {
+                const u32 dn = __shfl_down_sync(0xFFFFFFFFu, cs_mid & 1u, 1);
+                lm |= ((cs_mid >> 1) | ((lane < 31 ? dn : 0u) << 31)) & ~dm;
+            }
+            const u32 cnt = __popc(lm);
             const u32 incl = warp_incl_scan(cnt);
             const u32 tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
             const u32 excl = incl - cnt;
@@ -1027,7 +1145,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             const u32 half0 = __shfl_sync(0xFFFFFFFFu, excl, 16); // delimiters in the first 512 bytes
             for (int ph = 0; ph < (dense ? 2 : 1); ph++) {
                 if (!dense || (ph == 0) == (lane < 16)) {
-                    u32 m = dm;
+                    u32 m = lm;
                     unsigned short *o = dl + excl - ((dense && ph) ? half0 : 0u);
                     while (m) {
                         const u32 p = __ffs(m) - 1; m &= m - 1;
@@ -1132,6 +1250,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
             }
             // the next tile sees this tile's last delimiter at a negative position
             carry_prev = first_prev - kTile < -(1 << 30) ? -(1 << 30) : first_prev - kTile;
+            lmod = lmod_next;
         }
     }
     // ---- per-warp results

@@ -219,7 +219,7 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     if (c.long_table_log2 == 0) c.long_table_log2 = 18;
     if (c.arena_bytes == 0) c.arena_bytes = 256ull << 20;
     if (c.short_table_log2 < 10 || c.short_table_log2 > 32 || c.long_table_log2 < 10 || c.long_table_log2 > 34 ||
-        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT)) {
+        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT) || (c.flags & ~WC_FLAG_STRICT_REF) != 0) {
         e->err = "wc_config out of range";
         return WC_ERR_INVALID;
     }
@@ -465,6 +465,7 @@ static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_pie
     wc::Launch L;
     L.buf = dev; L.n = n; L.base = e->cfg.base_offset + e->consumed;
     L.tiles_per_warp = (u32)tpw; L.last_piece = last_piece; L.negate = 0;
+    L.strict = (e->cfg.flags & WC_FLAG_STRICT_REF) != 0;
     L.ws = e->d_ws; L.n_ws = e->n_ws;
     memset(&L.em, 0, sizeof(L.em));
     if (e->sort_mode) {
@@ -1445,7 +1446,7 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
             const u64 tpw = (tiles + warps - 1) / warps;
             wc::Launch L;
             L.buf = (const uint8_t *)dev_text; L.n = n; L.base = 0; L.tiles_per_warp = (u32)tpw;
-            L.last_piece = 1; L.negate = 0; L.ws = ws; L.n_ws = n_ws;
+            L.last_piece = 1; L.negate = 0; L.strict = 0; L.ws = ws; L.n_ws = n_ws;
             wc::count_kernel<<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
             L.negate = 1;
             wc::count_kernel<<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);

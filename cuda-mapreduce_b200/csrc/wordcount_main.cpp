@@ -14,19 +14,21 @@
 
 static void usage() {
     fprintf(stderr,
-            "usage: wordcount [FILE] [--no-echo] [--mode=ref|exact] [--chunk-bytes=N] [--device=N] [--json]\n"
-            "  FILE defaults to test.txt in the current directory, as in the reference.\n");
+            "usage: wordcount [FILE] [--no-echo] [--strict-ref] [--mode=ref|exact] [--chunk-bytes=N] [--device=N] [--json]\n"
+            "  FILE defaults to test.txt in the current directory, as in the reference.\n"
+            "  --strict-ref: read lines in pieces of 99 bytes like the reference's fgets(szLine, 100) does.\n");
 }
 
 // printf("%s", szLine) for every fgets(szLine, 100) chunk, up to and including the one that stops
 // the reference (main.cu:176-186).  Lines are echoed whole here (capacity lifted: SURVEY.md A.2 L5);
-// for lines of <= 99 bytes that is the same byte stream.
-static void echo_input(const std::vector<char> &d) {
+// for lines of <= 99 bytes that is the same byte stream.  cap = 99 (--strict-ref): the reference's own pieces.
+static void echo_input(const std::vector<char> &d, size_t cap) {
     size_t pos = 0;
     const size_t n = d.size();
     while (pos < n) {
-        const char *nl = (const char *)memchr(d.data() + pos, '\n', n - pos);
-        const size_t clen = nl ? (size_t)(nl - (d.data() + pos)) + 1 : n - pos;
+        const size_t span = (cap && n - pos > cap) ? cap : n - pos;
+        const char *nl = (const char *)memchr(d.data() + pos, '\n', span);
+        const size_t clen = nl ? (size_t)(nl - (d.data() + pos)) + 1 : span;
         const size_t slen = strnlen(d.data() + pos, clen);
         fwrite(d.data() + pos, 1, slen, stdout);
         if (slen < 2) break;
@@ -43,6 +45,7 @@ int main(int argc, char **argv) {
         const char *a = argv[i];
         if (!strcmp(a, "--no-echo")) echo = false;
         else if (!strcmp(a, "--json")) json = true;
+        else if (!strcmp(a, "--strict-ref")) cfg.flags |= WC_FLAG_STRICT_REF;
         else if (!strncmp(a, "--mode=", 7)) cfg.mode = !strcmp(a + 7, "exact") ? WC_MODE_EXACT : WC_MODE_REF;
         else if (!strncmp(a, "--chunk-bytes=", 14)) cfg.chunk_bytes = strtoull(a + 14, nullptr, 10);
         else if (!strncmp(a, "--device=", 9)) cfg.device = atoi(a + 9);
@@ -60,7 +63,7 @@ int main(int argc, char **argv) {
         while ((k = fread(buf, 1, sizeof(buf), f)) > 0) data.insert(data.end(), buf, buf + k);
         fclose(f);
     }
-    if (present && echo) echo_input(data);
+    if (present && echo) echo_input(data, (cfg.flags & WC_FLAG_STRICT_REF) ? 99 : 0);
 
     wc_engine *e = nullptr;
     wc_result *r = nullptr;

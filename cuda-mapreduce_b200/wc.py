@@ -9,6 +9,7 @@ ROOT = os.path.dirname(HERE)
 MODE_REF = 0
 MODE_EXACT = 1
 PATH_AUTO, PATH_HASH, PATH_SORT = 0, 1, 2
+FLAG_STRICT_REF = 1
 
 
 def lib_path():
@@ -179,11 +180,12 @@ class Engine:
     """with Engine(mode=...) as e: e.feed(bytes); res = e.finish()"""
 
     def __init__(self, mode=MODE_REF, device=0, chunk_bytes=0, short_table_log2=0, long_table_log2=0,
-                 arena_bytes=0, base_offset=0, path=0):
+                 arena_bytes=0, base_offset=0, path=0, strict_ref=False):
         L = lib()
         cfg = Config()
         L.wc_config_default(C.byref(cfg))
         cfg.mode, cfg.device, cfg.base_offset, cfg.path = mode, device, base_offset, path
+        cfg.flags = FLAG_STRICT_REF if strict_ref else 0
         if chunk_bytes:
             cfg.chunk_bytes = chunk_bytes
         if short_table_log2:

@@ -57,6 +57,14 @@ typedef enum wc_status {
 #define WC_PATH_HASH 1 /* shared-memory table spilling to a global open-addressing table */
 #define WC_PATH_SORT 2 /* radix sort of (hash, offset, length) + segmented reduce */
 
+/* wc_config.flags */
+#define WC_FLAG_STRICT_REF 1u /* read lines the way main.cu does: in pieces of at most 99 bytes (fgets(szLine, 100),
+                                 main.cu:175,179).  On a line longer than that the word that straddles a piece edge
+                                 loses its head, 0x0D / 0x00 hide only the rest of the piece, and a one-byte piece
+                                 (line length = 1 mod 99) stops the input (main.cu:185).  Without the flag a line is
+                                 one piece however long it is; the two agree on every line of at
+                                 most 99 bytes. */
+
 typedef struct wc_config {
     uint32_t struct_size;      /* = sizeof(wc_config) */
     int32_t device;            /* CUDA device ordinal */
@@ -67,7 +75,7 @@ typedef struct wc_config {
     uint32_t long_table_log2;  /* global table slots for words of 17+ bytes (0: 2^18) */
     uint64_t arena_bytes;      /* device byte store for the 17+ byte words (0: 256 MiB) */
     uint64_t base_offset;      /* offset of this engine's first byte in the whole input (shards) */
-    uint32_t flags;            /* reserved, 0 */
+    uint32_t flags;            /* WC_FLAG_* */
     uint32_t reserved;
 } wc_config;
 

@@ -52,6 +52,7 @@ def lib():
         L.orc_literal.argtypes = [u8p, C.c_size_t, C.c_int, C.POINTER(Result)]
         L.orc_fast.argtypes = [u8p, C.c_size_t, C.c_int, C.POINTER(Result)]
         L.orc_fast_mt.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.POINTER(Result)]
+        L.orc_fast_cap.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.POINTER(Result)]
         L.orc_free.argtypes = [C.POINTER(Result)]
         L.orc_flush_formula.argtypes = [u8p, C.c_size_t, u8p]
         L.orc_flush_formula.restype = C.c_uint64
@@ -119,6 +120,12 @@ def literal(data, linecap=LINECAP_REF, render=False):
 
 def fast(data, mode=MODE_REF, render=False, keep_rows=True):
     return _run(lib().orc_fast, data, mode, render_linecap=LINECAP_INF if render else None,
+                keep_rows=keep_rows)
+
+
+def fast_cap(data, mode=MODE_REF, linecap=LINECAP_REF, render=False, keep_rows=True):
+    """orc_fast with the reference's own 99-byte chunking (the engine's strict-ref mode)."""
+    return _run(lib().orc_fast_cap, data, mode, linecap, render_linecap=linecap if render else None,
                 keep_rows=keep_rows)
 
 

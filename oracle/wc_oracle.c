@@ -301,13 +301,17 @@ static void finalize(fmap *m, int mode, orc_result *out) {
     free(acc); free(best); free(stk); free(owner); free(v);
 }
 
-int orc_fast(const uint8_t *data, size_t n, int mode, orc_result *out) {
+int orc_fast_cap(const uint8_t *data, size_t n, int mode, int linecap, orc_result *out) {
     memset(out, 0, sizeof(*out));
     fmap m; fmap_init(&m, data, n, 1u << 16);
-    split(data, n, 0, ORC_LINECAP_INF, fast_emit, &m, out);
+    split(data, n, 0, linecap, fast_emit, &m, out);
     finalize(&m, mode, out);
     free(m.e);
     return 0;
+}
+
+int orc_fast(const uint8_t *data, size_t n, int mode, orc_result *out) {
+    return orc_fast_cap(data, n, mode, ORC_LINECAP_INF, out);
 }
 
 /* ---- multi-threaded variant: line-aligned slices, per-thread tables ------- */

@@ -58,6 +58,12 @@ int orc_literal(const uint8_t *data, size_t n, int linecap, orc_result *out);
  * post-pass.  linecap is always ORC_LINECAP_INF here. */
 int orc_fast(const uint8_t *data, size_t n, int mode, orc_result *out);
 
+/* The same with the reference's own chunking: linecap = ORC_LINECAP_REF reads lines in pieces of at
+ * most 99 bytes like fgets(szLine, 100) does (main.cu:175,179), so a word that straddles a piece
+ * edge loses its head, CR / NUL hide only the rest of the piece, and a piece of one byte stops the
+ * input (main.cu:185).  Checked against orc_literal(linecap) in tests/test_oracle.py. */
+int orc_fast_cap(const uint8_t *data, size_t n, int mode, int linecap, orc_result *out);
+
 /* orc_fast over `nthreads` line-aligned slices, merged.  Same results. */
 int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_result *out);
 

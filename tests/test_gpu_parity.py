@@ -11,7 +11,7 @@ import pytest
 
 from conftest import ROOT, load_pkg
 from oracle import orc as O
-from test_oracle import ALPHABET, DELIMS, random_text
+from test_oracle import ALPHABET, DELIMS, long_line_text, random_text
 
 pytestmark = pytest.mark.gpu
 
@@ -415,6 +415,69 @@ def test_large_result_storage(pkg, monkeypatch):
     with pkg.Engine(chunk_bytes=1 << 20, **SMALL) as e:
         check_against_oracle(e, data)
         check_against_oracle(e, data[:1000])
+
+
+def check_strict(engine, data, what=""):
+    """strict-ref engine against the oracle with the reference's own 99-byte chunking."""
+    engine.reset()
+    engine.feed(data)
+    got = engine.finish()
+    exp = O.fast_cap(data, O.MODE_REF, O.LINECAP_REF)
+    assert (got.stats["n_flush"], got.stats["n_empty"], got.stats["stop"]) == (exp.n_flush, exp.n_empty, exp.stop), what
+    assert got.pairs() == exp.pairs(), what
+    assert got.total == exp.total, what
+    assert got.firsts == [f for _, _, f in exp.rows], what
+    assert got.stats["n_lost_empty"] == exp.n_lost_empty, what
+    return got
+
+
+def test_strict_ref_mode(pkg, golden):
+    """WC_FLAG_STRICT_REF: lines are read in pieces of 99 bytes like main.cu's
+    fgets(szLine, 100) reads them.  With it the engine reproduces the reference's stdout on EVERY golden
+    vector, the long-line quirks included, and matches the chunked oracle on fuzzed long lines."""
+    rng = random.Random(515)
+    with pkg.Engine(strict_ref=True, chunk_bytes=1 << 20, **SMALL) as e:
+        for name, data, expect in golden:
+            if data is None:
+                continue
+            got = check_strict(e, data, what=name)
+            assert expect.endswith(got.rendered), name
+        for i in range(200):
+            data = long_line_text(rng, rng.randint(1, 500), weird=rng.choice([0.0, 0.03, 0.15]))
+            check_strict(e, data, what=("fuzz", i, data))
+        # piece starts at every position relative to the 32-byte lane and the 1 KiB tile: a short first
+        # line of `shift` bytes moves a long line (and its piece edges) across them
+        word = b"abcdefghij"
+        for shift in list(range(2, 70)) + [99, 100, 198, 924, 925, 926, 1023, 1024, 1025]:
+            first = (b"x" * (shift - 1) + b"\n") if shift <= 99 else (b"y " * (shift // 2))[: shift - 1] + b"\n"
+            long_line = b" ".join(word[: rng.randint(1, 10)] for _ in range(400))
+            data = first + long_line + b"\n" + b"tail words here\n"
+            check_strict(e, data, what=("shift", shift))
+        # a line whose length is 1 mod 99 ends in a one-byte piece: the reference stops there (main.cu:185)
+        for extra in (0, 1, 2, 98, 99, 100):
+            data = b"ok line\n" + b"a" * 50 + b" " + b"b" * (48 + extra) + b"\nafter the long line\n"
+            check_strict(e, data, what=("len", extra))
+        # kills are per piece: a CR / NUL in the first piece of a long line does not hide the later pieces
+        data = b"w1 w2\rhidden " + b"c" * 90 + b" seen again\nnext\n" + b"n1\0hid " + b"d" * 95 + b" back\n"
+        check_strict(e, data, what="kills per piece")
+    # ragged feeds and small streaming chunks
+    with pkg.Engine(strict_ref=True, chunk_bytes=4096, **SMALL) as e:
+        data = long_line_text(rng, 20000, weird=0.01).replace(b"\n\n", b"\n").replace(b"\0", b"")
+        check_strict(e, data, what="chunked")
+
+
+def test_strict_ref_cli(pkg, golden):
+    """wordcount --strict-ref prints what the reference prints on the long-line golden vectors too."""
+    exe = os.path.join(ROOT, "cuda-mapreduce_b200", "wordcount")
+    picked = [g for g in golden if g[1] is not None and O.fast(g[1]).max_line > 99][:12]
+    assert picked
+    with tempfile.TemporaryDirectory() as td:
+        for name, data, expect in picked:
+            with open(os.path.join(td, "test.txt"), "wb") as f:
+                f.write(data)
+            r = subprocess.run([exe, "--strict-ref"], cwd=td, capture_output=True, timeout=120)
+            assert r.returncode == 0, (name, r.stderr)
+            assert r.stdout == expect, name
 
 
 def test_word_table_grows_instead_of_overflowing(pkg):

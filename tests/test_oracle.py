@@ -150,3 +150,38 @@ def test_live_reference_fuzz():
         for name, data in mg.fuzz_vectors(150, 777):
             ref = O.run_reference_cpu(data, td)
             assert O.literal(data, O.LINECAP_REF, render=True).stdout == ref, (name, data)
+
+
+def long_line_text(rng, n_tokens, weird=0.05):
+    """Text whose lines often exceed the reference's 99-byte fgets buffer (main.cu:175,179)."""
+    out = bytearray()
+    for _ in range(n_tokens):
+        out += rng.choice(ALPHABET + [b"w" * rng.randint(1, 120), b"zz", b"q"])
+        r = rng.random()
+        if r < weird:
+            out += rng.choice([b"\r", b"\0", b"\r\n", b"\n\n"])
+        elif r < weird + 0.04:
+            out += b"\n"
+        else:
+            out += rng.choice([b" ", b" ", b"  "])
+    return bytes(out)
+
+
+def test_fast_cap_matches_literal_with_the_reference_line_buffer(golden):
+    """The strict-ref oracle (99-byte chunks): orc_fast_cap == orc_literal(99) on
+    every golden vector -- whose stdout it must also reproduce, long lines included -- and on fuzzed
+    text with long lines, CR, NUL and blank lines."""
+    for name, data, expect in golden:
+        if data is None:
+            continue
+        a, b = O.literal(data, O.LINECAP_REF), O.fast_cap(data, O.MODE_REF, O.LINECAP_REF, render=True)
+        assert a.pairs() == b.pairs() and a.total == b.total, name
+        assert (a.n_flush, a.n_empty, a.n_lost_empty, a.stop) == (b.n_flush, b.n_empty, b.n_lost_empty, b.stop), name
+        assert b.stdout == expect, name
+    rng = random.Random(4242)
+    for i in range(150):
+        data = long_line_text(rng, rng.randint(1, 400), weird=rng.choice([0.0, 0.03, 0.15]))
+        a, b = O.literal(data, O.LINECAP_REF), O.fast_cap(data, O.MODE_REF, O.LINECAP_REF)
+        assert a.pairs() == b.pairs() and a.total == b.total, i
+        assert (a.n_flush, a.n_empty, a.n_lost_empty, a.stop) == (b.n_flush, b.n_empty, b.n_lost_empty, b.stop), i
+
