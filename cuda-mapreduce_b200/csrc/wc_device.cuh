@@ -19,10 +19,10 @@ typedef unsigned long long u64;
 typedef unsigned int u32;
 
 #ifndef WC_WARPS
-#define WC_WARPS 24
+#define WC_WARPS 28
 #endif
 #ifndef WC_CONSUMERS
-#define WC_CONSUMERS 6
+#define WC_CONSUMERS 8
 #endif
 #ifndef WC_DRAIN
 #define WC_DRAIN 64
