@@ -48,6 +48,7 @@ struct wc_engine {
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_counted[2] = {nullptr, nullptr};
     int ring = 0;
     std::vector<uint8_t> carry; // bytes after the last '\n' seen so far (an unfinished line)
+    uint8_t *h_stage[2] = {nullptr, nullptr}; // pinned staging for callers that feed pageable memory (allocated on demand)
 
     // sort path (WC_PATH_SORT): one record per word of 1..16 bytes, sorted and reduced in wc_finish
     bool sort_mode = false;
@@ -184,6 +185,7 @@ void wc_destroy(wc_engine *e) {
     if (e->d_status) cudaFree(e->d_status);
     if (e->d_ws) cudaFree(e->d_ws);
     if (e->d_cursors) cudaFree(e->d_cursors);
+    for (int i = 0; i < 2; i++) if (e->h_stage[i]) cudaFreeHost(e->h_stage[i]);
     if (e->peer.area) cudaFree(e->peer.area);
     if (e->peer.mapped && e->peer.ipc) cudaIpcCloseMemHandle(e->peer.mapped);
     if (e->peer.d_cur) cudaFree(e->peer.d_cur);
@@ -501,6 +503,7 @@ static int ensure_chunks(wc_engine *e) {
         CK(cudaEventCreateWithFlags(&e->ev_copied[i], cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&e->ev_counted[i], cudaEventDisableTiming));
         CK(cudaEventRecord(e->ev_counted[i], e->stream));
+        CK(cudaEventRecord(e->ev_copied[i], e->copy_stream));
     }
     return WC_OK;
 }
@@ -512,6 +515,20 @@ static int feed_piece(wc_engine *e, const uint8_t *src, size_t n, int last_piece
     if (rc != WC_OK) return rc;
     if (n <= e->chunk_cap) {
         const int s = e->ring;
+        // Pageable source (malloc'd buffers, std::vector, the carry): cudaMemcpyAsync would stage it through
+        // the driver's small bounce buffer on this thread.  Copy it into a pinned slot with several threads
+        // instead and let the DMA engine take it from there, overlapped with the next slot's fill.
+        if (n >= ((size_t)1 << 20)) {
+            cudaPointerAttributes at;
+            const bool pageable = cudaPointerGetAttributes(&at, src) != cudaSuccess || at.type == cudaMemoryTypeUnregistered;
+            (void)cudaGetLastError();
+            if (pageable) {
+                if (!e->h_stage[s]) CK(cudaMallocHost((void **)&e->h_stage[s], e->chunk_cap + 64));
+                CK(cudaEventSynchronize(e->ev_copied[s])); // the copy that last read this slot is done
+                wc::parallel_copy(e->h_stage[s], src, n);
+                src = e->h_stage[s];
+            }
+        }
         CK(cudaStreamWaitEvent(e->copy_stream, e->ev_counted[s], 0)); // the kernel that read this buffer is done
         CK(cudaMemcpyAsync(e->d_chunk[s], src, n, cudaMemcpyHostToDevice, e->copy_stream));
         CK(cudaEventRecord(e->ev_copied[s], e->copy_stream));

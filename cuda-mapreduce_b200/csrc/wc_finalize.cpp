@@ -14,7 +14,7 @@ wc_result::~wc_result() { free(big_rows); free(big_blob); }
 namespace wc {
 
 void parallel_copy(void *dst, const void *src, size_t bytes) {
-    const size_t kMin = (size_t)32 << 20;
+    const size_t kMin = (size_t)4 << 20;
     unsigned hw = std::thread::hardware_concurrency();
     size_t nt = bytes / kMin;
     if (nt > 8) nt = 8;

@@ -480,6 +480,18 @@ def test_strict_ref_cli(pkg, golden):
             assert r.stdout == expect, name
 
 
+def test_feed_from_pageable_memory_goes_through_pinned_staging(pkg):
+    """wc_feed of ordinary (pageable) host memory: pieces of 1 MiB and more are copied into a pinned
+    slot by several threads and sent from there; the slots are reused across pieces and jobs."""
+    rng = random.Random(44)
+    base = random_text(rng, 400000, weird=0.0).replace(b"\n\n", b"\n")
+    data = base * 4 + b"last words without newline"
+    assert len(data) > (6 << 20)
+    with pkg.Engine(chunk_bytes=2 << 20, **SMALL) as e:
+        for _ in range(2):
+            check_against_oracle(e, data)
+
+
 def test_word_table_grows_instead_of_overflowing(pkg):
     """A word table far too small for the vocabulary: words it cannot take go to the overflow log, the
     host re-hashes into a larger table and replays the log -- nothing is lost (wc_engine.cu

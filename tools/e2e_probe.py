@@ -23,3 +23,19 @@ for chunk in (0, 16 << 20, 32 << 20, 128 << 20):
             e.sync(); t3 = time.perf_counter()
             r = e.finish(keep_rows=False); t4 = time.perf_counter()
         print("chunk %4d MiB: reset %.2f feed %.2f sync %.2f finish %.2f total %.2f ms" % (chunk >> 20, (t1-t0)*1e3, (t2-t1)*1e3, (t3-t2)*1e3, (t4-t3)*1e3, (t4-t0)*1e3))
+# the same from pageable host memory (what a caller with a malloc'd buffer or a std::vector gives wc_feed)
+pageable = torch.empty(n, dtype=torch.uint8)
+pageable.copy_(host)
+with pkg.Engine(short_table_log2=18, long_table_log2=12) as e:
+    for it in range(4):
+        t0 = time.perf_counter(); e.reset(); e.feed((pageable.data_ptr(), n)); e.sync(); t1 = time.perf_counter()
+        r = e.finish(keep_rows=False); t2 = time.perf_counter()
+    print("pageable source: feed+sync %.2f ms (%.1f GB/s) finish %.2f ms" % ((t1-t0)*1e3, n/(t1-t0)/1e9, (t2-t1)*1e3))
+import ctypes as C
+rt = C.CDLL("libcudart.so.12")
+t0 = time.perf_counter()
+for _ in range(2):
+    rt.cudaMemcpy(C.c_void_p(dev.data_ptr()), C.c_void_p(pageable.data_ptr()), C.c_size_t(n), 1)
+dt = (time.perf_counter() - t0) / 2
+print("plain cudaMemcpy from pageable memory: %.2f ms (%.1f GB/s)" % (dt*1e3, n/dt/1e9))
+
