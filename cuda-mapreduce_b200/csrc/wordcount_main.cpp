@@ -7,7 +7,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/wc.h"
@@ -36,6 +39,61 @@ static void echo_input(const std::vector<char> &d, size_t cap) {
     }
 }
 
+// --no-echo: the file never sits in memory as a whole.  A reader thread fills pinned slabs
+// (wc_host_alloc) while the main thread feeds the previous one to the engine, so reading the file,
+// the PCIe copy and the count kernel overlap.  Returns a wc_status.
+static int stream_file(wc_engine *e, FILE *f) {
+    constexpr size_t kSlab = (size_t)64 << 20;
+    constexpr int kSlabs = 3;
+    char *slab[kSlabs] = {nullptr, nullptr, nullptr};
+    size_t fill[kSlabs] = {0, 0, 0};
+    for (int i = 0; i < kSlabs; i++)
+        if (wc_host_alloc((void **)&slab[i], kSlab) != WC_OK) {
+            for (int j = 0; j < i; j++) wc_host_free(slab[j]);
+            return WC_ERR_NOMEM;
+        }
+    std::mutex mu;
+    std::condition_variable cv;
+    int produced = 0, consumed = 0; // slabs filled / slabs fed
+    bool eof = false;
+    std::thread reader([&] {
+        for (;;) {
+            int s;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return produced - consumed < kSlabs; });
+                s = produced % kSlabs;
+            }
+            const size_t k = fread(slab[s], 1, kSlab, f);
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                if (k == 0) eof = true; else { fill[s] = k; produced++; }
+            }
+            cv.notify_all();
+            if (k == 0) return;
+        }
+    });
+    int rc = WC_OK;
+    for (;;) {
+        int s;
+        {
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return produced > consumed || eof; });
+            if (produced == consumed) break;
+            s = consumed % kSlabs;
+        }
+        if (rc == WC_OK) rc = wc_feed(e, slab[s], fill[s]); // (after an error: keep draining so that the reader ends)
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            consumed++;
+        }
+        cv.notify_all();
+    }
+    reader.join();
+    for (int i = 0; i < kSlabs; i++) wc_host_free(slab[i]);
+    return rc;
+}
+
 int main(int argc, char **argv) {
     const char *path = "test.txt";
     bool echo = true, json = false;
@@ -56,20 +114,23 @@ int main(int argc, char **argv) {
     printf("Input Data:\n"); // main.cu:166
     std::vector<char> data;
     bool present = false;
-    if (FILE *f = fopen(path, "rb")) { // main.cu:167 ("rt" is the same on Linux)
+    FILE *f = fopen(path, "rb"); // main.cu:167 ("rt" is the same on Linux)
+    if (f && echo) { // the echo needs the text itself: small inputs, read whole
         present = true;
         char buf[1 << 16];
         size_t k;
         while ((k = fread(buf, 1, sizeof(buf), f)) > 0) data.insert(data.end(), buf, buf + k);
         fclose(f);
+        f = nullptr;
+        echo_input(data, (cfg.flags & WC_FLAG_STRICT_REF) ? 99 : 0);
     }
-    if (present && echo) echo_input(data, (cfg.flags & WC_FLAG_STRICT_REF) ? 99 : 0);
 
     wc_engine *e = nullptr;
     wc_result *r = nullptr;
     int rc = wc_create(&e, &cfg);
     if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(nullptr)); return 1; }
     if (present) rc = wc_feed(e, data.data(), data.size());
+    else if (f) { rc = stream_file(e, f); fclose(f); }
     if (rc == WC_OK) rc = wc_finish(e, &r);
     if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(e)); wc_destroy(e); return 1; }
     const size_t need = wc_result_render(r, nullptr, 0);

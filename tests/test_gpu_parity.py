@@ -492,6 +492,25 @@ def test_feed_from_pageable_memory_goes_through_pinned_staging(pkg):
             check_against_oracle(e, data)
 
 
+def test_cli_streams_large_files_without_echo(pkg):
+    """wordcount FILE --no-echo never holds the file in memory: a reader thread fills pinned slabs while
+    the previous one is fed.  160 MB of config-2 text (several slabs), output against the oracle."""
+    from tools.corpus import Corpus
+    exe = os.path.join(ROOT, "cuda-mapreduce_b200", "wordcount")
+    n = 160 << 20
+    data = Corpus(2, total_bytes=n).bytes()
+    exp = O.fast_mt(data)
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "big.txt")
+        data.tofile(path)
+        r = subprocess.run([exe, path, "--no-echo"], capture_output=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+    lines = r.stdout.split(b"\n")
+    assert lines[0] == b"Input Data:" and lines[1] == b"-" * 26 and lines[-2] == b"Total Count:%d" % exp.total
+    rows = [tuple(l.rsplit(b"\t", 1)) for l in lines[2:-3]]
+    assert rows == [(w, b"%d" % c) for w, c in exp.pairs()]
+
+
 def test_word_table_grows_instead_of_overflowing(pkg):
     """A word table far too small for the vocabulary: words it cannot take go to the overflow log, the
     host re-hashes into a larger table and replays the log -- nothing is lost (wc_engine.cu
