@@ -107,6 +107,10 @@ def workload_params(name, n_gpus):
         total = CONFIGS[3]["bytes"]
         return dict(config=3, total=total, per_gpu=total // n_gpus, s_log2=22, l_log2=14,
                     label="config3: Zipf(1.1) text, 1M-word vocabulary, 1.6e10 B over all GPUs")
+    if name == "config4":
+        total = CONFIGS[4]["bytes"]
+        return dict(config=4, total=total, per_gpu=total // n_gpus, s_log2=22, l_log2=14,
+                    label="config4: Zipf(1.1) text, 1M-word vocabulary, 1e11 B over all GPUs (strong scaling)")
     if name == "config5":
         per_gpu = CONFIGS[5]["bytes"]
         return dict(config=5, total=per_gpu * n_gpus, per_gpu=per_gpu, s_log2=30, l_log2=16,
@@ -173,6 +177,8 @@ def main():
     ap.add_argument("--table-log2", type=int, default=0, help="override the word table size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    ap.add_argument("--device-corpus", action="store_true",
+                    help="generate the corpus straight into device memory (default for shards above 4.5 GiB); no e2e leg")
     ap.add_argument("--strict-ref", action="store_true",
                     help="WC_FLAG_STRICT_REF: read lines in 99-byte pieces like the reference's fgets (same results on these corpora)")
     ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
@@ -212,9 +218,22 @@ def main():
     corpus = Corpus(wp["config"], total_bytes=wp["total"])
     lo, hi = shard_range(wp["total"], corpus.block, rank, world)
     nbytes = hi - lo
-    host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
-    corpus.fill(host.numpy(), lo, nbytes)
-    dev = host.cuda(non_blocking=False)
+    device_corpus = args.device_corpus or nbytes > (9 << 29)  # > 4.5 GiB per GPU: generate straight into HBM
+    if device_corpus:
+        # configs 3 / 4: the shard is written by tools/corpus_gpu.cu (byte-identical to the host generator,
+        # tests/test_gpu_parity.py); only a 1 GB sample exists on the host (cpu_baseline), so there is no e2e leg
+        torch.cuda.set_device(local_rank)
+        dev = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+        corpus.fill_device(dev.data_ptr(), lo, nbytes)
+        hs = min(nbytes, 1 << 30)
+        host = torch.empty(hs, dtype=torch.uint8).pin_memory()
+        if rank == 0 and not args.no_cpu_baseline:
+            corpus.fill(host.numpy(), lo, hs)
+        args.no_e2e = True
+    else:
+        host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+        corpus.fill(host.numpy(), lo, nbytes)
+        dev = host.cuda(non_blocking=False)
 
     eng = pkg.Engine(device=local_rank, short_table_log2=wp["s_log2"], long_table_log2=wp["l_log2"], base_offset=lo,
                      path={"auto": 0, "hash": 1, "sort": 2}[args.path], strict_ref=args.strict_ref)
@@ -321,8 +340,9 @@ def main():
     achieved = nbytes / (kernel_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-        "data": "synthetic",
+        "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak" if args.workload in ("config2", "config5") else "strong", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic" + (" (generated on the device)" if device_corpus else ""),
         "config": {"workload": wp["label"], "bytes_per_gpu": nbytes, "words_per_gpu": words,
                    "distinct_words": res.stats["n_distinct"], "deferred_1to8B_words": res.stats["n_spilled"],
                    "words_9B_plus": res.stats["n_long_words"],
@@ -343,7 +363,7 @@ def main():
     }
     if not args.no_cpu_baseline:
         from oracle import orc
-        sample = min(nbytes, 1 << 30)
+        sample = min(nbytes, 1 << 30, host.numel())
         view = host.numpy()[:sample]
         t0 = time.perf_counter()
         rb = orc.fast(view, keep_rows=False)

@@ -511,6 +511,18 @@ def test_cli_streams_large_files_without_echo(pkg):
     assert rows == [(w, b"%d" % c) for w, c in exp.pairs()]
 
 
+def test_device_corpus_generator_is_byte_identical_to_the_host_one(pkg):
+    """tools/corpus_gpu.cu (bench tooling for the 16 GB / 100 GB corpora) against tools/corpus.c."""
+    import torch
+    from tools.corpus import Corpus
+    for config, total, off, n in ((2, (9 << 20) + 12345, 0, (9 << 20) + 12345), (3, 64 << 20, 5 << 20, 6 << 20),
+                                  (4, (3 << 20) + 2, 1 << 20, (2 << 20) + 2)):
+        c = Corpus(config, total_bytes=total)
+        dev = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        c.fill_device(dev.data_ptr(), off, n)
+        assert np.array_equal(dev.cpu().numpy(), c.bytes(off, n)), config
+
+
 def test_word_table_grows_instead_of_overflowing(pkg):
     """A word table far too small for the vocabulary: words it cannot take go to the overflow log, the
     host re-hashes into a larger table and replays the log -- nothing is lost (wc_engine.cu

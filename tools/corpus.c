@@ -305,6 +305,16 @@ const uint8_t *corpus_word(const corpus *c, uint32_t rank, uint32_t *len) {
     return c->words[rank];
 }
 
+/* The tables the Zipf block writer reads, for the device port of it (tools/corpus_gpu.cu). */
+int corpus_tables(const corpus *c, const uint8_t **words, const uint8_t **lens, const uint32_t **by_len,
+                  uint64_t *fill_max, const uint32_t **alias, const uint32_t **thresh, uint32_t *vocab,
+                  uint64_t *text_seed) {
+    if (c->kind != 0) return -1;
+    *words = &c->words[0][0]; *lens = c->lens; *by_len = c->by_len; *fill_max = c->fill_max;
+    *alias = c->alias; *thresh = c->thresh; *vocab = c->vocab; *text_seed = c->text_seed;
+    return 0;
+}
+
 typedef struct { const corpus *c; uint8_t *dst; uint64_t off, total; size_t n; uint64_t b0, b1; int tid, nt; } fill_job;
 
 static void *fill_main(void *arg) {

@@ -42,8 +42,27 @@ def lib():
         L.corpus_fill.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int]
         L.corpus_word.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.corpus_word.restype = C.c_void_p
+        L.corpus_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 8
         _lib = L
     return _lib
+
+
+_gpu_lib = None
+
+
+def gpu_lib():
+    """tools/libcorpus_gpu.so (built by `make -C tools`; nvcc cross-compiles without a GPU)."""
+    global _gpu_lib
+    if _gpu_lib is None:
+        so = os.path.join(HERE, "libcorpus_gpu.so")
+        src = os.path.join(HERE, "corpus_gpu.cu")
+        if (not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src)) and os.path.exists("/usr/local/cuda/bin/nvcc"):
+            subprocess.run(["make", "-C", HERE, "libcorpus_gpu.so"], check=True, capture_output=True)
+        L = C.CDLL(so)
+        L.corpus_gpu_fill.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32,
+                                      C.c_uint64, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]
+        _gpu_lib = L
+    return _gpu_lib
 
 
 class Corpus:
@@ -78,6 +97,23 @@ class Corpus:
         if rc != 0:
             raise ValueError("corpus_fill rc=%d (range must be block aligned; block=%d)" % (rc, self.block))
         return out
+
+    def fill_device(self, dev_ptr, off=0, n=None):
+        """The same bytes written straight into device memory by tools/corpus_gpu.cu (Zipf kinds only):
+        configs 3 and 4 are too large to generate and copy on the host for every run."""
+        if n is None:
+            n = self.total - off
+        gl = gpu_lib()
+        words, lens, by_len, alias, thresh = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        fill_max, text_seed, vocab = C.c_uint64(), C.c_uint64(), C.c_uint32()
+        rc = lib().corpus_tables(self.h, C.byref(words), C.byref(lens), C.byref(by_len), C.byref(fill_max),
+                                 C.byref(alias), C.byref(thresh), C.byref(vocab), C.byref(text_seed))
+        if rc != 0:
+            raise ValueError("fill_device: only the Zipf corpora have a device generator")
+        rc = gl.corpus_gpu_fill(words, lens, by_len, fill_max, alias, thresh, vocab, text_seed, C.c_void_p(int(dev_ptr)),
+                                off, n, self.total)
+        if rc != 0:
+            raise ValueError("corpus_gpu_fill rc=%d" % rc)
 
     def bytes(self, off=0, n=None, nthreads=0):
         if n is None:
