@@ -291,7 +291,25 @@ def main():
     kernel_ms = ksum / args.steps
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- the whole job's result once more, outside any timed region: row count, total and a digest of
+    # the rows, so that runs of the same workload on different GPU counts can be compared line by line
+    result_check = None
+    want_digest = args.workload != "config5"  # (2.9e8 rows there; decided the same way on every rank)
+    step_device()
+    if rank == 0:
+        full = eng.finish(keep_rows=False)
+        result_check = {"rows": full.n_rows, "total": full.total, "n_flush": full.stats["n_flush"], "stop": full.stats["stop"]}
+    if want_digest:
+        step_device()
+        if rank == 0:
+            import hashlib
+            full = eng.finish(keep_rows=True)
+            h = hashlib.sha256()
+            for w, c in full.rows:
+                h.update(w + b"\t%d\n" % c)
+            result_check["rows_sha256"] = h.hexdigest()
     if world > 1:
+        barrier()
         eng.reset()
         eng.count_device(dev.data_ptr(), nbytes, last_piece=(rank == world - 1))
     res = eng.finish(keep_rows=False)  # this rank's shard alone: its words for the words/s figure
@@ -358,6 +376,7 @@ def main():
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": nbytes},
         "e2e": ({"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": d2h,
                  "ms_per_step": te.item() * 1e3} if e2e_steps else None),
+        "result_check": result_check,
         "gpu_launches": int(launches) * args.steps,
         "clocks": clocks,
     }
