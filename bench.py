@@ -227,7 +227,7 @@ def main():
         corpus.fill_device(dev.data_ptr(), lo, nbytes)
         hs = min(nbytes, 1 << 30)
         host = torch.empty(hs, dtype=torch.uint8).pin_memory()
-        if rank == 0 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline:
             corpus.fill(host.numpy(), lo, hs)
         args.no_e2e = True
     else:
@@ -380,7 +380,7 @@ def main():
         "gpu_launches": int(launches) * args.steps,
         "clocks": clocks,
     }
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:  # (the CPU baseline is timed at N = 1 only)
         from oracle import orc
         sample = min(nbytes, 1 << 30, host.numel())
         view = host.numpy()[:sample]
