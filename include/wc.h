@@ -113,7 +113,10 @@ WC_API int wc_feed(wc_engine *e, const void *bytes, size_t n);
 /* Count `n` bytes that are already in device memory (16-byte aligned, same
  * device).  The piece must start at a line start of the input; every piece but
  * the last must end with '\n'.  Asynchronous on the engine's stream; the
- * buffer must stay valid until wc_sync()/wc_finish(). */
+ * buffer must stay valid until wc_sync()/wc_finish().  Bytes 8..15 of longer
+ * words are fetched in aligned 8-byte units, so up to 7 bytes past `n` (to the
+ * next multiple of 8) may be read, never used: the allocation must cover them,
+ * as every cudaMalloc'd buffer does. */
 WC_API int wc_count_device(wc_engine *e, const void *dev_bytes, size_t n, int last_piece);
 
 /* No more input will come: counts the unterminated last line, if any (its final word is dropped
