@@ -87,6 +87,7 @@ struct wc_engine {
     u64 fed = 0;      // bytes given to wc_feed / wc_count_device
     u64 launches = 0;
     u64 pieces = 0;      // pieces launched since the last reset
+    bool settle_due = false; // the table check for the last launched piece is still to be done
     u64 grows = 0;
 
     // timing: per piece, events before the count kernel, after it, and after its roll-back companion
@@ -278,7 +279,7 @@ int wc_reset(wc_engine *e) {
     if (rc != WC_OK) return rc;
     e->carry.clear();
     e->job_stats_set = false; e->job_bytes = 0;
-    e->consumed = 0; e->fed = 0; e->launches = 0; e->pieces = 0; e->device_ms = 0; e->count_kernel_ms = 0;
+    e->consumed = 0; e->fed = 0; e->launches = 0; e->pieces = 0; e->settle_due = false; e->device_ms = 0; e->count_kernel_ms = 0;
     for (auto &p : e->ev_used) { e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.mid); e->ev_pool.push_back(p.b); }
     e->ev_used.clear();
     return WC_OK;
@@ -532,20 +533,23 @@ static int feed_piece(wc_engine *e, const uint8_t *src, size_t n, int last_piece
         CK(cudaStreamWaitEvent(e->copy_stream, e->ev_counted[s], 0)); // the kernel that read this buffer is done
         CK(cudaMemcpyAsync(e->d_chunk[s], src, n, cudaMemcpyHostToDevice, e->copy_stream));
         CK(cudaEventRecord(e->ev_copied[s], e->copy_stream));
+        // Keep the word table ahead of the vocabulary: after each of the first pieces, and then every
+        // eighth, wait for the piece and grow the table / replay the overflow log if needed.  One chunk
+        // can never overflow the log (it holds more records than a chunk has words).  The wait for the
+        // PREVIOUS piece happens here, while this piece's copy is already running.
+        if (e->settle_due) {
+            e->settle_due = false;
+            CK(cudaStreamSynchronize(e->stream));
+            rc = settle_tables(e);
+            if (rc != WC_OK) return rc;
+        }
         CK(cudaStreamWaitEvent(e->stream, e->ev_copied[s], 0));
         rc = launch_piece(e, e->d_chunk[s], n, last_piece);
         if (rc != WC_OK) return rc;
         CK(cudaEventRecord(e->ev_counted[s], e->stream));
         e->ring ^= 1;
-        // Keep the word table ahead of the vocabulary: after each of the first pieces, and then every
-        // eighth, wait for the piece and grow the table / replay the overflow log if needed.  One chunk
-        // can never overflow the log (it holds more records than a chunk has words).
         e->pieces++;
-        if (e->pieces <= 4 || (e->pieces & 7) == 0) {
-            CK(cudaStreamSynchronize(e->stream));
-            rc = settle_tables(e);
-            if (rc != WC_OK) return rc;
-        }
+        if (e->pieces <= 4 || (e->pieces & 7) == 0) e->settle_due = true;
         return WC_OK;
     }
     // a single line longer than the chunk: give it a buffer of its own
