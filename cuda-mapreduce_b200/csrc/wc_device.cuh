@@ -280,10 +280,10 @@ __device__ __forceinline__ ulonglong2 cas128(ulonglong2 *addr, ulonglong2 cmp, u
     return old;
 }
 
-// The global word table is probed a BUCKET of four slots (64 bytes) at a time: all four keys are
-// read at once, so a lookup costs one memory round trip unless the whole bucket belongs to other
-// words (probability ~ load^4) -- with 64 lookups in flight per consumer warp, a scheme in which a
-// few percent of them need a second trip would make every batch wait for it.
+// The global word table can be probed a BUCKET of kBucket slots at a time (all keys of the bucket are
+// read at once).  The shipping build uses 1: the table is kept below half full, so a second probe
+// is rare, and a 4-slot bucket measured 40 % slower (its 16 key registers per lookup went through
+// the stack).  WC_BUCKET is a build knob for experiments.
 #ifndef WC_BUCKET
 #define WC_BUCKET 1
 #endif
@@ -637,7 +637,8 @@ __device__ __noinline__ StrictOut strict_exact(uint4 va, uint4 vb, u32 starts, u
 //   9..16 bytes : fetch bytes 8..15 from the text, count in the global word table;
 //   17+ bytes   : the arena-backed long table.
 // Ring protocol (a bounded multi-producer multi-consumer queue with a sequence number per cell):
-// producers reserve positions with one atomicAdd on `tail` per warp and round; position p belongs to
+// a producer warp gathers its records in a staging area of its own and reserves ring positions with
+// one atomicAdd on `tail` per 33..64 of them (flush_stage); position p belongs to
 // cell p % kDefRing in lap p / kDefRing.  A cell's last word says whose turn it is:
 //     lap                       (bit 31 clear)  the cell is free and waits for the writer of that lap
 //     1<<31 | lap<<16 | t<<15 | len15  (bit 31 set)  the record of that lap is in the cell
