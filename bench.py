@@ -168,8 +168,8 @@ def ncu_traffic(workload, nbytes):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="config2")
     ap.add_argument("--bytes", type=int, default=0, help="override the per-GPU input size (profiling / sweeps)")
@@ -336,7 +336,7 @@ def main():
                 return None
         return eng.finish(keep_rows=False)
 
-    e2e_steps = 0 if args.no_e2e else max(3, args.steps // 2)
+    e2e_steps = 0 if args.no_e2e else min(50, max(3, args.steps // 2))
     if e2e_steps:
         step_e2e()
     barrier()
