@@ -27,6 +27,19 @@ typedef unsigned int u32;
 #ifndef WC_DRAIN
 #define WC_DRAIN 64
 #endif
+// further build knobs (experiments): staging records per producer warp, ring cells, consumer sleep (ns)
+#ifndef WC_STAGE
+#define WC_STAGE 64
+#endif
+#ifndef WC_RING
+#define WC_RING 1024
+#endif
+#ifndef WC_SLEEP0
+#define WC_SLEEP0 400
+#endif
+#ifndef WC_SLEEP1
+#define WC_SLEEP1 1200
+#endif
 constexpr int kSub = 512;                  // bytes per sub-tile: 32 lanes x 16 B
 constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = WC_WARPS;           // warps per CTA
@@ -38,11 +51,11 @@ constexpr int kRingBytes = 2 * kBufBytes;  // per producer warp: two buffers, th
 constexpr int kDlCap = 512;                // per producer warp: delimiter list entries
 constexpr int kDlBytes = kDlCap * 2;
 constexpr int kDrainBatch = WC_DRAIN;      // deferred words a consumer warp takes at a time (WC_DRAIN / 32 per lane)
-constexpr u32 kDefRing = 1024;             // per CTA: ring of deferred-word records (16 bytes each)
+constexpr u32 kDefRing = WC_RING;             // per CTA: ring of deferred-word records (16 bytes each)
 constexpr u64 kNone = ~0ull;
 constexpr u32 kMaxWordProbes = 128;        // longer probe chains in the global word table mean: grow it
 
-constexpr u32 kStageCap = 64;              // per producer warp: deferred records gathered before they go to the ring
+constexpr u32 kStageCap = WC_STAGE;              // per producer warp: deferred records gathered before they go to the ring
 constexpr int kStageBytes = kStageCap * 16;
 constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kStageBytes;
 constexpr size_t kDefRingBytes = (size_t)kDefRing * 16;
@@ -744,7 +757,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
         for (const u32 last = b + kDrainBatch - 1;;) {
             if ((lds_volatile_u32(&ring[last & (kDefRing - 1)].w) >> 16) == (0x8000u | ring_lap(last))) break;
             if (lds_volatile_u32(&ctl->done) == (u32)kProducers || ++spins > (1u << 23)) break;
-            __nanosleep(spins < 2 ? 400 : 1200); // a batch takes a few microseconds to fill: do not burn issue slots polling
+            __nanosleep(spins < 2 ? WC_SLEEP0 : WC_SLEEP1); // a batch takes a few microseconds to fill: do not burn issue slots polling
         }
 #endif
         u32 polls = spins > (1u << 23) ? spins : 0; // (counted per pass of this loop, which the vote below keeps in step)
