@@ -367,48 +367,72 @@ __device__ __forceinline__ u32 word_insert(const Tables &T, u64 k0, u64 k1, u32 
     return word_insert_at(T, k0, k1, delta, first_abs, slot, load_bucket(T, slot));
 }
 
+// -------------------------------------------------------- mappers
+// The reference is nominally a MapReduce skeleton: its mapper() (main.cu:37-54) turns every word into
+// the pair (word, 1) and a maintainer may swap it.  Here the mapper is a policy of the kernel: a
+// byte-wise, length-preserving transform of the word's bytes that is applied wherever they are read
+// (key extraction from the tile, bytes 8..15 fetched by the consumers, hashing / comparing / storing
+// the 17+ byte words).  It must map 0x00 to 0x00 and must not produce or consume delimiters.  Adding
+// one: a struct with map4 / map8, an entry in wc.h's WC_MAP_* and in launch_count_kernel() (wc_engine.cu).
+struct MapIdentity { // main.cu's own mapper: the word as it is
+    __device__ __forceinline__ static u32 map4(u32 x) { return x; }
+    __device__ __forceinline__ static u64 map8(u64 x) { return x; }
+};
+struct MapLowerAscii { // 'A'..'Z' -> 'a'..'z': a case-insensitive word count
+    __device__ __forceinline__ static u32 map4(u32 x) {
+        const u32 h = x & 0x7F7F7F7Fu;
+        const u32 up = ~x & 0x80808080u & ((h + 0x3F3F3F3Fu) ^ (h + 0x25252525u)); // 0x80 where 'A' <= byte <= 'Z'
+        return x | (up >> 2);
+    }
+    __device__ __forceinline__ static u64 map8(u64 x) {
+        return (u64)map4((u32)x) | ((u64)map4((u32)(x >> 32)) << 32);
+    }
+};
+
 // -------------------------------------------------------- global long table (17+ bytes)
 
 // Very long words (the adversarial corpus has some of 1 MiB) are handled by one lane, so their loops
 // keep 16 independent 8-byte loads in flight per step: they are bound by load latency, not by arithmetic.
+template <class Map>
 __device__ __forceinline__ u64 long_hash(const uint8_t *buf, u64 start, u64 len) {
     u64 h = 0x9E3779B97F4A7C15ull ^ (len * 0xFF51AFD7ED558CCDull);
     u64 i = 0;
     for (; i + 128 <= len; i += 128) {
         u64 v[16];
 #pragma unroll
-        for (int j = 0; j < 16; j++) v[j] = load8_unaligned(buf, start + i + 8 * j);
+        for (int j = 0; j < 16; j++) v[j] = Map::map8(load8_unaligned(buf, start + i + 8 * j));
 #pragma unroll
         for (int j = 0; j < 16; j++) { h = (h ^ v[j]) * 0x9FB21C651E98DF25ull; h ^= h >> 32; }
     }
     for (; i + 8 <= len; i += 8) {
-        h = (h ^ load8_unaligned(buf, start + i)) * 0x9FB21C651E98DF25ull;
+        h = (h ^ Map::map8(load8_unaligned(buf, start + i))) * 0x9FB21C651E98DF25ull;
         h ^= h >> 32;
     }
     if (i < len) {
-        u64 v = load8_unaligned(buf, start + i, (u32)(len - i));
+        u64 v = Map::map8(load8_unaligned(buf, start + i, (u32)(len - i)));
         h = (h ^ v) * 0x9FB21C651E98DF25ull;
         h ^= h >> 32;
     }
     return mix64(h);
 }
 
+template <class Map>
 __device__ __forceinline__ bool long_equal(const Tables &T, u64 unit, const uint8_t *buf, u64 start, u64 len) {
     if (__ldcg(&T.arena[unit]) != len) return false;
     u64 i = 0;
     for (; i + 64 <= len; i += 64) {
         u64 a[8], b[8];
 #pragma unroll
-        for (int j = 0; j < 8; j++) { a[j] = __ldcg(&T.arena[unit + 1 + (i >> 3) + j]); b[j] = load8_unaligned(buf, start + i + 8 * j); }
+        for (int j = 0; j < 8; j++) { a[j] = __ldcg(&T.arena[unit + 1 + (i >> 3) + j]); b[j] = Map::map8(load8_unaligned(buf, start + i + 8 * j)); }
         u64 diff = 0;
 #pragma unroll
         for (int j = 0; j < 8; j++) diff |= a[j] ^ b[j];
         if (diff) return false;
     }
     for (; i + 8 <= len; i += 8)
-        if (__ldcg(&T.arena[unit + 1 + (i >> 3)]) != load8_unaligned(buf, start + i)) return false;
+        if (__ldcg(&T.arena[unit + 1 + (i >> 3)]) != Map::map8(load8_unaligned(buf, start + i))) return false;
     if (i < len) {
-        u64 v = load8_unaligned(buf, start + i, (u32)(len - i));
+        u64 v = Map::map8(load8_unaligned(buf, start + i, (u32)(len - i)));
         if (__ldcg(&T.arena[unit + 1 + (i >> 3)]) != v) return false;
     }
     return true;
@@ -416,10 +440,11 @@ __device__ __forceinline__ bool long_equal(const Tables &T, u64 unit, const uint
 
 // A word of 17+ bytes at buf[start, start+len).  Never waits on another thread: a new word is
 // first written to the arena, then published with one CAS of the slot word.  Returns 1 if new.
+template <class Map>
 __device__ __noinline__ u32 long_insert(const Tables *Tp, const uint8_t *buf, u64 start, u64 len, u64 delta,
                                         u64 first_abs) {
     const Tables &T = *Tp;
-    const u64 h = long_hash(buf, start, len);
+    const u64 h = long_hash<Map>(buf, start, len);
     const u64 mask = (1ull << T.x_log2) - 1;
     const u64 tag = h >> 40;
     u64 slot = h & mask;
@@ -437,19 +462,19 @@ __device__ __noinline__ u32 long_insert(const Tables *Tp, const uint8_t *buf, u6
                 for (; i + 128 <= len; i += 128) {
                     u64 v[16];
 #pragma unroll
-                    for (int j = 0; j < 16; j++) v[j] = load8_unaligned(buf, start + i + 8 * j);
+                    for (int j = 0; j < 16; j++) v[j] = Map::map8(load8_unaligned(buf, start + i + 8 * j));
 #pragma unroll
                     for (int j = 0; j < 16; j++) T.arena[idx + 1 + (i >> 3) + j] = v[j];
                 }
-                for (; i + 8 <= len; i += 8) T.arena[idx + 1 + (i >> 3)] = load8_unaligned(buf, start + i);
-                if (i < len) T.arena[idx + 1 + (i >> 3)] = load8_unaligned(buf, start + i, (u32)(len - i));
+                for (; i + 8 <= len; i += 8) T.arena[idx + 1 + (i >> 3)] = Map::map8(load8_unaligned(buf, start + i));
+                if (i < len) T.arena[idx + 1 + (i >> 3)] = Map::map8(load8_unaligned(buf, start + i, (u32)(len - i)));
                 __threadfence();
                 my_ref = (tag << 40) | idx;
             }
             r = atom_cas_u64(&T.x_refs[slot], 0ull, my_ref);
             if (r == 0) { is_new = 1; break; }
         }
-        if ((r >> 40) == tag && long_equal(T, r & ((1ull << 40) - 1), buf, start, len)) break;
+        if ((r >> 40) == tag && long_equal<Map>(T, r & ((1ull << 40) - 1), buf, start, len)) break;
         slot = (slot + 1) & mask;
         if (probes > 4096 || probes >= mask) { red_or_u32(&T.st->err, kErrLongFull); return 0; }
     }
@@ -727,6 +752,7 @@ __device__ __forceinline__ void flush_stage(const uint4 *stage, u32 n, uint4 *ri
     __syncwarp(); // the staged records have been read: the area may be overwritten
 }
 
+template <class Map>
 #ifdef WC_EXP_NOINLINE
 __device__ __noinline__
 #else
@@ -832,7 +858,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
             const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
             const u64 end = cta_base + rec[j].z; // buffer-relative offset of the delimiter
             if (todo & (1u << j))
-                n_wnew += word_insert_at(T, k0, rec[j].w > 8 ? load8_finish(raw[j]) : 0ull, delta, Lp->base + end, slot[j], key[j]);
+                n_wnew += word_insert_at(T, k0, rec[j].w > 8 ? Map::map8(load8_finish(raw[j])) : 0ull, delta, Lp->base + end, slot[j], key[j]);
         }
         // 17+ byte words last and on their own: a function call between the loads above and their use
         // would push every loaded key through the stack.
@@ -846,7 +872,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
 #pragma unroll
                 for (int q = 1; q < R; q++) if (q == j) r = rec[q];
                 const u64 end = cta_base + r.z;
-                if (r.w > 16) n_xnew += long_insert(Tp, Lp->buf, end - r.w, r.w, delta, Lp->base + end);
+                if (r.w > 16) n_xnew += long_insert<Map>(Tp, Lp->buf, end - r.w, r.w, delta, Lp->base + end);
             }
         }
 #ifdef WC_PROFILE
@@ -900,6 +926,7 @@ __device__ __forceinline__ void fetch_tile(const Launch &L, u64 tile, unsigned c
 
 extern __shared__ __align__(16) unsigned char wc_smem[];
 
+template <class Map>
 __global__ void __launch_bounds__(kThreads, 1)
 count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T) {
     uint4 *tab = reinterpret_cast<uint4 *>(wc_smem);
@@ -958,7 +985,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
 
     const u64 cta_base = (u64)blockIdx.x * kProducers * L.tiles_per_warp * kTile; // buffer-relative
     if (warp >= (u32)kProducers) { // ---- consumer warps: everything that needs global memory
-        consume_deferred(def_ring, &s_ctl, &L, &T, cta_base, tab);
+        consume_deferred<Map>(def_ring, &s_ctl, &L, &T, cta_base, tab);
     } else { // ---- producer warps: tokenize and count
 
     // per-warp shared memory: [two tile buffers] [delimiter list]
@@ -1190,7 +1217,8 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     const u32 w0 = r[0], w1 = r[1], w2 = r[2];
                     const u64 keep = ~0ull >> (8u * (8u - (u32)(rlen > 8 ? 8 : rlen))); // the first min(len, 8) bytes
                     const u32 sh = (idx & 3) * 8;
-                    const u32 klo = __funnelshift_r(w0, w1, sh) & (u32)keep, khi = __funnelshift_r(w1, w2, sh) & (u32)(keep >> 32);
+                    const u32 klo = Map::map4(__funnelshift_r(w0, w1, sh) & (u32)keep),
+                              khi = Map::map4(__funnelshift_r(w1, w2, sh) & (u32)(keep >> 32));
 
                     if (L.em.cursor != nullptr) { // ---- sort path: write the word out instead of counting it
                         const bool emit = word && len <= 16 && !L.negate; // (what lies after STOP is dropped at the end)
@@ -1203,8 +1231,8 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                                 u32 k1lo = 0, k1hi = 0;
                                 if (len > 8) { // bytes 8..15
                                     const u64 keep1 = ~0ull >> (8u * (16u - (u32)len));
-                                    k1lo = __funnelshift_r(w2, r[3], sh) & (u32)keep1;
-                                    k1hi = __funnelshift_r(r[3], r[4], sh) & (u32)(keep1 >> 32);
+                                    k1lo = Map::map4(__funnelshift_r(w2, r[3], sh) & (u32)keep1);
+                                    k1hi = Map::map4(__funnelshift_r(r[3], r[4], sh) & (u32)(keep1 >> 32));
                                 }
                                 const u64 k0 = (u64)klo | ((u64)khi << 32), k1 = (u64)k1lo | ((u64)k1hi << 32);
                                 L.em.key[at] = make_ulonglong2(k0, k1); // (sort keys are derived from these at the end)

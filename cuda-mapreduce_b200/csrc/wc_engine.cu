@@ -222,7 +222,7 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     if (c.long_table_log2 == 0) c.long_table_log2 = 18;
     if (c.arena_bytes == 0) c.arena_bytes = 256ull << 20;
     if (c.short_table_log2 < 10 || c.short_table_log2 > 32 || c.long_table_log2 < 10 || c.long_table_log2 > 34 ||
-        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT) || (c.flags & ~WC_FLAG_STRICT_REF) != 0) {
+        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT) || (c.flags & ~WC_FLAG_STRICT_REF) != 0 || c.mapper > WC_MAP_LOWER_ASCII) {
         e->err = "wc_config out of range";
         return WC_ERR_INVALID;
     }
@@ -236,7 +236,8 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     e->grid = e->num_sms; // persistent: one CTA per SM, the shared-memory table fills the SM
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
-    CK(cudaFuncSetAttribute(wc::count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::kSmemTotal));
+    CK(cudaFuncSetAttribute(wc::count_kernel<wc::MapIdentity>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::kSmemTotal));
+    CK(cudaFuncSetAttribute(wc::count_kernel<wc::MapLowerAscii>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::kSmemTotal));
     CK(cudaMalloc((void **)&e->d_status, sizeof(wc::Status)));
     CK(cudaMallocHost((void **)&e->h_status, sizeof(wc::Status)));
     e->T.st = e->d_status;
@@ -458,6 +459,17 @@ static int finish_sorted(wc_engine *e, u64 stop_abs, std::string &blob, std::vec
     return WC_OK;
 }
 
+// The tokenizer/count kernel with the engine's mapper (wc_config.mapper -> a policy of the kernel).
+static void launch_count_kernel(wc_engine *e, const wc::Launch &L) {
+    switch (e->cfg.mapper) {
+    case WC_MAP_LOWER_ASCII:
+        wc::count_kernel<wc::MapLowerAscii><<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+        break;
+    default:
+        wc::count_kernel<wc::MapIdentity><<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+    }
+}
+
 // Launches the forward count of one piece and its roll-back/summary companion on e->stream.
 static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
     if (n == 0) return WC_OK;
@@ -484,10 +496,10 @@ static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_pie
         else CK(cudaEventCreate(ev));
     }
     CK(cudaEventRecord(a, e->stream));
-    wc::count_kernel<<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+    launch_count_kernel(e, L);
     CK(cudaEventRecord(mid, e->stream));
     L.negate = 1;
-    wc::count_kernel<<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+    launch_count_kernel(e, L);
     CK(cudaGetLastError());
     CK(cudaEventRecord(b, e->stream));
     e->ev_used.push_back(wc_engine::EvTriple{a, mid, b});
@@ -1434,7 +1446,7 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
             if ((ce = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) {
                 rc = static_fail(WC_ERR_CUDA, "cudaDeviceGetAttribute", ce); break;
             }
-            if ((ce = cudaFuncSetAttribute(wc::count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            if ((ce = cudaFuncSetAttribute(wc::count_kernel<wc::MapIdentity>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)wc::kSmemTotal)) != cudaSuccess) {
                 rc = static_fail(WC_ERR_CUDA, "cudaFuncSetAttribute", ce); break;
             }
@@ -1468,9 +1480,9 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
             wc::Launch L;
             L.buf = (const uint8_t *)dev_text; L.n = n; L.base = 0; L.tiles_per_warp = (u32)tpw;
             L.last_piece = 1; L.negate = 0; L.strict = 0; L.ws = ws; L.n_ws = n_ws;
-            wc::count_kernel<<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
+            wc::count_kernel<wc::MapIdentity><<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
             L.negate = 1;
-            wc::count_kernel<<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
+            wc::count_kernel<wc::MapIdentity><<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
         }
         static_end_kernel<<<1, 32, 0, stream>>>(st, (u64 *)dev_counters);
         if ((ce = cudaGetLastError()) != cudaSuccess) { rc = static_fail(WC_ERR_CUDA, "kernel launch", ce); break; }

@@ -77,7 +77,7 @@ __global__ void import_long_kernel(Tables T, const LongRecord *meta, u64 n, cons
     for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
         const LongRecord r = meta[i];
         if (r.len == 0 || r.count == 0) continue;
-        made += long_insert(&T, blob, r.blob_off, r.len, r.count, r.first);
+        made += long_insert<MapIdentity>(&T, blob, r.blob_off, r.len, r.count, r.first);
     }
     made = __reduce_add_sync(0xFFFFFFFFu, made);
     if ((threadIdx.x & 31) == 0 && made) atomicAdd(&T.st->x_entries, (u64)made);
@@ -187,7 +187,7 @@ __global__ void import_areas_kernel(Tables T, const __grid_constant__ ImportList
         for (u64 i = tid; i < L.n_x[a]; i += stride) {
             const LongRecord r = L.x[a][i];
             if (r.len == 0 || r.count == 0) continue;
-            made_x += long_insert(&T, L.blob[a], r.blob_off, r.len, r.count, r.first);
+            made_x += long_insert<MapIdentity>(&T, L.blob[a], r.blob_off, r.len, r.count, r.first);
         }
     }
     made_w = __reduce_add_sync(0xFFFFFFFFu, made_w);

@@ -17,7 +17,7 @@
 
 static void usage() {
     fprintf(stderr,
-            "usage: wordcount [FILE] [--no-echo] [--strict-ref] [--mode=ref|exact] [--chunk-bytes=N] [--device=N] [--json]\n"
+            "usage: wordcount [FILE] [--no-echo] [--strict-ref] [--map=identity|lower] [--mode=ref|exact] [--chunk-bytes=N] [--device=N] [--json]\n"
             "  FILE defaults to test.txt in the current directory, as in the reference.\n"
             "  --strict-ref: read lines in pieces of 99 bytes like the reference's fgets(szLine, 100) does.\n");
 }
@@ -104,6 +104,8 @@ int main(int argc, char **argv) {
         if (!strcmp(a, "--no-echo")) echo = false;
         else if (!strcmp(a, "--json")) json = true;
         else if (!strcmp(a, "--strict-ref")) cfg.flags |= WC_FLAG_STRICT_REF;
+        else if (!strcmp(a, "--map=lower")) cfg.mapper = WC_MAP_LOWER_ASCII;
+        else if (!strcmp(a, "--map=identity")) cfg.mapper = WC_MAP_IDENTITY;
         else if (!strncmp(a, "--mode=", 7)) cfg.mode = !strcmp(a + 7, "exact") ? WC_MODE_EXACT : WC_MODE_REF;
         else if (!strncmp(a, "--chunk-bytes=", 14)) cfg.chunk_bytes = strtoull(a + 14, nullptr, 10);
         else if (!strncmp(a, "--device=", 9)) cfg.device = atoi(a + 9);

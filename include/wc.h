@@ -65,6 +65,14 @@ typedef enum wc_status {
                                  one piece however long it is; the two agree on every line of at
                                  most 99 bytes. */
 
+/* wc_config.mapper: what a word is mapped to before it is counted.  The reference's mapper()
+ * (main.cu:37-54) emits (word, 1) for the word as it is: WC_MAP_IDENTITY.  Other mappers are
+ * byte-wise, length-preserving transforms applied inside the kernel wherever a word's bytes are read;
+ * they are compiled-in policies (csrc/wc_device.cuh, "mappers"), this field selects one.  The reducer
+ * side of the skeleton is wc_config.mode. */
+#define WC_MAP_IDENTITY 0u
+#define WC_MAP_LOWER_ASCII 1u /* 'A'..'Z' counted as 'a'..'z' (a case-insensitive word count) */
+
 typedef struct wc_config {
     uint32_t struct_size;      /* = sizeof(wc_config) */
     int32_t device;            /* CUDA device ordinal */
@@ -76,7 +84,7 @@ typedef struct wc_config {
     uint64_t arena_bytes;      /* device byte store for the 17+ byte words (0: 256 MiB) */
     uint64_t base_offset;      /* offset of this engine's first byte in the whole input (shards) */
     uint32_t flags;            /* WC_FLAG_* */
-    uint32_t reserved;
+    uint32_t mapper;           /* WC_MAP_* */
 } wc_config;
 
 /* Counters of one finished job; the same numbers the oracle reports. */

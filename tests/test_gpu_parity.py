@@ -523,6 +523,36 @@ def test_device_corpus_generator_is_byte_identical_to_the_host_one(pkg):
         assert np.array_equal(dev.cpu().numpy(), c.bytes(off, n)), config
 
 
+def test_mapper_policy_lower_ascii(pkg):
+    """wc_config.mapper: the reference's mapper emits (word, 1) for the word as it
+    is; WC_MAP_LOWER_ASCII folds 'A'..'Z' inside the kernel wherever word bytes are read (tile keys,
+    bytes 8..15, 17+ byte words).  A byte-wise map that leaves delimiters alone commutes with the
+    splitter, so the engine on the text must equal the oracle on the mapped text -- rows, first
+    offsets, prefix merges and all."""
+    rng = random.Random(77)
+    words = [b"The", b"the", b"THE", b"Then", b"tHEN", b"International", b"INTERNATIONAL", b"international",
+             b"AVeryVeryVeryLongWord_Over_16_Bytes", b"averyveryverylongword_over_16_bytes", b"MiXeD9\xc3\x89", b"A", b"a,",
+             b"Z" * 40, b"z" * 33, b"z" * 40, b"x"]
+    body = bytearray()
+    for _ in range(60000):
+        body += rng.choice(words) + rng.choice([b" ", b" ", b"\n", b"  ", b"\r\n"])
+    data = bytes(body).replace(b"\n\n", b"\n")
+    with pkg.Engine(mapper=pkg.MAP_LOWER_ASCII, chunk_bytes=1 << 20, **SMALL) as e:
+        for text in (data, data[:5000] + b"\n\n" + data[5000:9000], b"UPPER lower Upper\n"):
+            e.reset()
+            e.feed(text)
+            got = e.finish()
+            exp = O.fast(text.lower())  # bytes.lower() folds ASCII letters only
+            assert got.pairs() == exp.pairs() and got.total == exp.total
+            assert got.firsts == [f for _, _, f in exp.rows]
+            assert (got.stats["n_flush"], got.stats["n_empty"], got.stats["stop"]) == (exp.n_flush, exp.n_empty, exp.stop)
+    with pkg.Engine(mapper=pkg.MAP_LOWER_ASCII, mode=pkg.MODE_EXACT, path=pkg.PATH_SORT, chunk_bytes=1 << 20, **SMALL) as e:
+        e.feed(data)
+        got = e.finish()
+        exp = O.fast(data.lower(), O.MODE_EXACT)
+        assert got.pairs() == exp.pairs() and got.total == exp.total
+
+
 def test_word_table_grows_instead_of_overflowing(pkg):
     """A word table far too small for the vocabulary: words it cannot take go to the overflow log, the
     host re-hashes into a larger table and replays the log -- nothing is lost (wc_engine.cu
