@@ -55,6 +55,10 @@ constexpr u32 kDefRing = WC_RING;             // per CTA: ring of deferred-word 
 constexpr u64 kNone = ~0ull;
 constexpr u32 kMaxWordProbes = 128;        // longer probe chains in the global word table mean: grow it
 
+#ifndef WC_EXP_UNROLL
+#define WC_EXP_UNROLL 1
+#endif
+constexpr int kRoundUnroll = WC_EXP_UNROLL;      // word rounds unrolled by this much (experiment)
 constexpr u32 kStageCap = WC_STAGE;              // per producer warp: deferred records gathered before they go to the ring
 constexpr int kStageBytes = kStageCap * 16;
 constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kStageBytes;
@@ -1201,6 +1205,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
 #ifdef WC_EXP_NOROUNDS
                 for (u32 k0 = 0; k0 < total && relT == 0xFFFFFFF1u; k0 += 32) {
 #else
+#pragma unroll kRoundUnroll
                 for (u32 k0 = 0; k0 < total; k0 += 32) {
 #endif
                     const u32 k = k0 + lane;
