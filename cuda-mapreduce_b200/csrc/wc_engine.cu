@@ -17,6 +17,7 @@
 #include "wc_sort.cuh"
 #include <cub/cub.cuh>
 #include <chrono>
+#include <mutex>
 #include <unordered_map>
 #include "wc_finalize.h"
 #include "wc_reduce.cuh"
@@ -1367,12 +1368,13 @@ uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts) { return wc::k
 // and every buffer the results are written to.
 //
 // g_static_scratch lives in every GPU's memory from the moment the library is loaded there until
-// the process exits (kStaticScratchBytes, about 97 KiB).  In host code the name `g_static_scratch`
+// the process exits (kStaticScratchBytes, about 121 KiB).  In host code the name `g_static_scratch`
 // is only a handle for the symbol, not a device address, so the address the kernel needs is looked
 // up once per device with cudaGetSymbolAddress() while that device is current.
 namespace {
 
-constexpr u32 kStaticMaxWarps = 4096; // 256 SMs x 16 warps: more than any sm_100 part has
+constexpr u32 kStaticMaxSMs = 256;    // more than any sm_100 part has
+constexpr u32 kStaticMaxWarps = kStaticMaxSMs * wc::kProducers; // one WarpSummary per tokenizing warp
 constexpr size_t kStaticStatusBytes = 512;
 constexpr size_t kStaticScratchBytes = kStaticStatusBytes + sizeof(wc::WarpSummary) * kStaticMaxWarps;
 static_assert(sizeof(wc::Status) <= kStaticStatusBytes, "Status must fit its slot");
@@ -1386,6 +1388,7 @@ struct StaticDevice {
     int num_sms;
 };
 StaticDevice g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mu; // guards the first-call set-up of g_static_dev[] (host threads may race to it)
 thread_local char g_static_err[192];
 
 // Start-of-call state: everything zero except the "none yet" markers; arena unit 0 is never used.
@@ -1436,6 +1439,7 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
     if ((ce = cudaSetDevice(device)) != cudaSuccess) return static_fail(WC_ERR_CUDA, "cudaSetDevice", ce);
     int rc = WC_OK;
     do {
+        std::lock_guard<std::mutex> guard(g_static_mu);
         StaticDevice &sd = g_static_dev[device];
         if (!sd.ready) { // first call on this device: find the array's address here, raise the kernel's smem limit
             void *addr = nullptr;
@@ -1461,7 +1465,7 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
         wc::Status *st = (wc::Status *)sd.scratch;
         wc::WarpSummary *ws = (wc::WarpSummary *)(sd.scratch + kStaticStatusBytes);
         const size_t s_n = (size_t)1 << short_log2, l_n = (size_t)1 << long_log2;
-        wc::Tables T;
+        wc::Tables T{}; // (no overflow log here: ovf_log = nullptr, ovf_cap = 0 -> a full table raises err, counters[6])
         T.w_keys = (ulonglong2 *)dev_short_table; T.w_counts = (u64 *)dev_short_table + 2 * s_n;
         T.w_finv = (u64 *)dev_short_table + 3 * s_n; T.w_log2 = short_log2;
         T.x_refs = (u64 *)dev_long_table; T.x_counts = T.x_refs + l_n; T.x_finv = T.x_refs + 2 * l_n; T.x_log2 = long_log2;
@@ -1477,7 +1481,11 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
             const u64 tiles = (n + wc::kTile - 1) / wc::kTile;
             const u64 warps = (u64)sd.num_sms * wc::kProducers;
             const u64 tpw = (tiles + warps - 1) / warps;
-            wc::Launch L;
+            if (tpw * wc::kProducers * wc::kTile >= 0xFFFFFFF0ull) { // a CTA's range must fit 32-bit offsets (as in launch_piece)
+                rc = static_fail(WC_ERR_TOO_LARGE, "wc_count_device_static: text too large for this GPU's SM count", cudaSuccess);
+                break;
+            }
+            wc::Launch L{}; // (em.cursor = nullptr: the counting path, not the sort path's record emitter)
             L.buf = (const uint8_t *)dev_text; L.n = n; L.base = 0; L.tiles_per_warp = (u32)tpw;
             L.last_piece = 1; L.negate = 0; L.strict = 0; L.ws = ws; L.n_ws = n_ws;
             wc::count_kernel<wc::MapIdentity><<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);

@@ -246,7 +246,7 @@ WC_API int wc_peer_pull(wc_engine *root, wc_shard_stats *job_out);
  * that gave the whole device heap to their own pool, and hot paths where the device-wide stall of
  * cudaMalloc/cudaFree is not acceptable.  It runs the same tokenizer/count kernel as
  * wc_count_device(), but the kernel's working state sits in a fixed array inside the library image
- * (about 97 KiB, resident on every GPU that loads libwc.so until the process exits) and the caller
+ * (about 121 KiB, resident on every GPU that loads libwc.so until the process exits) and the caller
  * provides the text and every result buffer.  The call makes no cudaMalloc/cudaFree and no other
  * allocating call, on the device or on the host.
  *

@@ -3,7 +3,7 @@
  *
  * CPU restatement of /root/reference/main.cu's word count.  Parity: PINNED
  * against the reference's own source run on host cores (oracle/_ref/main_cpu)
- * -- tests/test_oracle_vs_reference.py and tests/golden/.
+ * -- tests/test_oracle.py and tests/golden/.
  *
  * Each function cites the reference lines it restates.  Nothing is copied: the
  * reference works on fixed-size structs (main.cu:16-33); this file works on

@@ -18,6 +18,7 @@ import numpy as np
 import pytest
 
 from conftest import load_pkg
+from oracle import orc
 from test_oracle import random_text
 
 pytestmark = pytest.mark.gpu
@@ -48,16 +49,17 @@ def decode_tables(short, long_, arena):
     return out
 
 
-def count_static(pkg, torch, data, bufs):
+def count_static(pkg, torch, data, bufs, s_log2=S_LOG2, decode=True):
     short, long_, arena, counters = bufs
     text = torch.frombuffer(bytearray(data) if data else bytearray(16), dtype=torch.uint8).cuda()
     rc = pkg.lib().wc_count_device_static(0, C.c_void_p(text.data_ptr()), len(data), C.c_void_p(short.data_ptr()),
-                                          S_LOG2, C.c_void_p(long_.data_ptr()), L_LOG2, C.c_void_p(arena.data_ptr()),
+                                          s_log2, C.c_void_p(long_.data_ptr()), L_LOG2, C.c_void_p(arena.data_ptr()),
                                           ARENA, C.c_void_p(counters.data_ptr()), None)
     assert rc == 0, pkg.lib().wc_static_last_error()
     torch.cuda.synchronize()
     u = lambda t: t.cpu().numpy().view(np.uint64)
-    return decode_tables(u(short), u(long_), u(arena)), [int(x) for x in u(counters)]
+    cnt = [int(x) for x in u(counters)]
+    return (decode_tables(u(short), u(long_), u(arena)) if decode else None), cnt
 
 
 def test_static_entry_point_matches_engine_twice_in_a_row():
@@ -81,8 +83,42 @@ def test_static_entry_point_matches_engine_twice_in_a_row():
             want = {w: (c, f) for (w, c), f in zip(ref.rows, ref.firsts)}
             assert counters[6] == 0, "table overflow flag"
             assert got == want
+            # ... and against the checker itself (exact mode: plain equality counts, first = flush offset)
+            exp = orc.fast(data, mode=orc.MODE_EXACT)
+            assert got == {w: (c, f) for (w, c, f) in exp.rows}
+            assert (counters[0], counters[1]) == (exp.n_flush, exp.n_empty)
             stop = counters[2] if counters[2] != NONE else len(data)
             assert (counters[0], counters[1], stop) == (ref.stats["n_flush"], ref.stats["n_empty"], ref.stats["stop"])
+
+
+def test_static_entry_point_reports_a_full_table_and_stays_inside_its_buffers():
+    """A word table too small for the text: the documented answer is err != 0 in counters[6]
+    (there is no overflow log on this path), nothing outside the caller's buffers is touched, and
+    the next call with a table of the right size is exact again."""
+    import torch
+    pkg = load_pkg()
+    rng = random.Random(77)
+    words = [b"w%05d" % i for i in range(6000)]          # 6000 distinct words against 1024 slots
+    data = b"\n".join(b" ".join(rng.choice(words) for _ in range(12)) for _ in range(4000)) + b"\n"
+    small_log2 = 10
+    guard = 1 << 12                                       # int64 sentinels before and after every buffer
+    def guarded(n):
+        t = torch.full((n + 2 * guard,), -1, dtype=torch.int64, device="cuda")
+        return t, t[guard:guard + n]
+    g_short, short = guarded(4 << S_LOG2)
+    g_long, long_ = guarded(3 << L_LOG2)
+    g_arena, arena = guarded(ARENA // 8)
+    g_cnt, counters = guarded(12)
+    # dirty the host stack a little before the call (the entry point builds its launch structs there)
+    _ = [rng.random() for _ in range(1000)]
+    _, cnt = count_static(pkg, torch, data, (short[:4 << small_log2], long_, arena, counters), s_log2=small_log2, decode=False)
+    assert cnt[6] != 0, "a 1024-slot table cannot hold 6000 words: err must be raised"
+    for g, inner in ((g_short, 4 << S_LOG2), (g_long, 3 << L_LOG2), (g_arena, ARENA // 8), (g_cnt, 12)):
+        assert bool((g[:guard] == -1).all()) and bool((g[guard + inner:] == -1).all()), "wrote outside a caller buffer"
+    assert bool((short[4 << small_log2:] == -1).all()), "wrote past the 1024-slot table"
+    got, cnt = count_static(pkg, torch, data, (short, long_, arena, counters))
+    exp = orc.fast(data, mode=orc.MODE_EXACT)
+    assert cnt[6] == 0 and got == {w: (c, f) for (w, c, f) in exp.rows}
 
 
 def test_static_entry_point_refuses_oversize_and_bad_arguments():
