@@ -101,7 +101,7 @@ def workload_params(name, n_gpus):
     from tools.corpus import CONFIGS
     if name == "config2":
         per_gpu = CONFIGS[2]["bytes"]  # 1e9 B per GPU (weak scaling for N > 1)
-        return dict(config=2, total=per_gpu * n_gpus, per_gpu=per_gpu, s_log2=18, l_log2=12,
+        return dict(config=2, total=per_gpu * n_gpus, per_gpu=per_gpu, s_log2=20, l_log2=12,
                     label="config2: Zipf(1.1) English-like text, 50k-word vocabulary, 1e9 B per GPU")
     if name == "config3":
         total = CONFIGS[3]["bytes"]

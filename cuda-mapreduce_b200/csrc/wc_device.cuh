@@ -94,7 +94,10 @@ struct Status {
 };
 
 struct Tables {
-    // words of 1..16 bytes: the key is the word itself, zero padded to 16 (exact by value)
+    // words of 1..16 bytes: the key is the word itself, zero padded to 16 (exact by value).  Three
+    // parallel arrays on purpose: the key sectors are read-only once a word is in, so the many readers
+    // of a frequent word's key never queue behind the atomics on its count (as one 32-byte slot per
+    // word the same kernel ran 1.6x slower: every key read waited for the read-modify-writes on its sector).
     ulonglong2 *w_keys;
     u64 *w_counts, *w_finv; // finv = ~first_offset, so 0 == unset and atomicMax keeps the min
     u32 w_log2;
@@ -156,6 +159,15 @@ __device__ __forceinline__ u64 mix64(u64 x) {
 // pick the slot).  Two multiply-adds; on the config-2 vocabulary it misses 0.8 % more often than a
 // full avalanche mix would, which costs less than the mix did.
 __host__ __device__ __forceinline__ u32 hash32(u32 lo, u32 hi) { return lo * 0x9E3779B1u + hi * 0x85EBCA77u; }
+// The same with a first multiplier that differs from CTA to CTA: two frequent words that share a slot of
+// the CTA's table (one of them then takes the slow path every time) do so in one CTA, not in all of them.
+__device__ __forceinline__ u32 hash32_of_cta(u32 lo, u32 hi) {
+#ifdef WC1_CTA_HASH
+    return lo * (0x9E3779B1u + 2u * (blockIdx.x * 0x632BE5ABu)) + hi * 0x85EBCA77u;
+#else
+    return hash32(lo, hi);
+#endif
+}
 
 // Flags (0x80 per byte) -> 16-bit mask, bit p = byte p of the 16 bytes (w0 lowest).
 // Two words share one multiply: (f1 | f0>>4) * (2^21+2^14+2^7+1) gathers the 8 flag bits
@@ -331,8 +343,11 @@ __device__ __forceinline__ u32 key_len8(u64 k0) { return 8u - ((u32)__clzll(k0) 
 // to the global table, starting at the bucket at `slot` whose keys the caller has already loaded.
 // Returns 1 if it claimed a new slot.
 __device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u64 delta, u64 first_abs, u32 slot,
-                                              Bucket b) {
+                                              Bucket b, u64 finv_seen = 0) {
+    // finv_seen: the home slot's ~first as the caller read it (0: not read).  It only ever grows, so if it
+    // already covers this offset the update below is not needed (one atomic less on the word's sector).
     const u32 mask = (u32)((1ull << T.w_log2) - 1);
+    const u32 slot_home = slot;
     u32 is_new = 0;
     for (u32 probes = 0;; ++probes) {
         u32 found = kBucket;
@@ -362,7 +377,7 @@ __device__ __forceinline__ u32 word_insert_at(const Tables &T, u64 k0, u64 k1, u
         b = load_bucket(T, slot);
     }
     red_add_u64(&T.w_counts[slot], delta); // both fire-and-forget
-    red_max_u64(&T.w_finv[slot], ~first_abs);
+    if (slot != slot_home || ~first_abs > finv_seen) red_max_u64(&T.w_finv[slot], ~first_abs);
     return is_new;
 }
 
@@ -821,11 +836,11 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
         // Decode, then issue every global read of the batch (the home bucket of each 1..16 byte word
         // and bytes 8..15 of the longer ones) BEFORE touching the shared-memory table: the claims below
         // run while those reads are in flight.  A word whose claim succeeds wasted one read.
-        u32 slot[R]; Bucket key[R]; Raw8 raw[R];
+        u32 slot[R]; Bucket key[R]; Raw8 raw[R]; u64 fin[R];
         u32 todo = 0; // bit j: record j goes to the global word table
 #pragma unroll
         for (int j = 0; j < R; j++) {
-            slot[j] = 0; raw[j] = Raw8{0, 0, 0, 8};
+            slot[j] = 0; raw[j] = Raw8{0, 0, 0, 8}; fin[j] = 0;
             if (!(live & (1u << j))) { rec[j] = make_uint4(0, 0, 0, 0); continue; }
             const bool slot_taken = (rec[j].w & 0x8000u) != 0;
             rec[j].w &= 0x7FFFu;                 // the word's length, saturated ...
@@ -836,6 +851,9 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
                 const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
                 slot[j] = word_home(T, k0, len);
                 key[j] = load_bucket(T, slot[j]);
+#ifdef WC1_FINV_HINT
+                fin[j] = __ldcg(&T.w_finv[slot[j]]);
+#endif
                 if (len > 8) raw[j] = load8_issue(Lp->buf, cta_base + rec[j].z - len + 8, len - 8);
                 if (len > 8 || slot_taken) todo |= 1u << j;
             }
@@ -846,7 +864,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
             if (len == 0 || len > 8) continue;
             if (todo & (1u << j)) { n_spill++; continue; }
             const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-            const u32 sidx = __umulhi(hash32(rec[j].x, rec[j].y), kSmemEntries);
+            const u32 sidx = __umulhi(hash32_of_cta(rec[j].x, rec[j].y), kSmemEntries);
             const u64 old = atoms_cas_u64(&tab[sidx], 0ull, k0);
             if (old == 0 || old == k0) {
                 u32 *cell = reinterpret_cast<u32 *>(&tab[sidx]);
@@ -862,7 +880,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
             const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
             const u64 end = cta_base + rec[j].z; // buffer-relative offset of the delimiter
             if (todo & (1u << j))
-                n_wnew += word_insert_at(T, k0, rec[j].w > 8 ? Map::map8(load8_finish(raw[j])) : 0ull, delta, Lp->base + end, slot[j], key[j]);
+                n_wnew += word_insert_at(T, k0, rec[j].w > 8 ? Map::map8(load8_finish(raw[j])) : 0ull, delta, Lp->base + end, slot[j], key[j], fin[j]);
         }
         // 17+ byte words last and on their own: a function call between the loads above and their use
         // would push every loaded key through the stack.
@@ -1262,7 +1280,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     }
 
                     // single-probe shared-memory table
-                    const u32 slot = __umulhi(hash32(klo, khi), kSmemEntries);
+                    const u32 slot = __umulhi(hash32_of_cta(klo, khi), kSmemEntries);
                     const uint4 ent = tab[slot];
                     const bool hit = word && len <= 8 && ent.x == klo && ent.y == khi;
                     const u32 rel = relT + (u32)e;

@@ -13,6 +13,7 @@
 
 #include "../../include/wc.h"
 #include "wc_device.cuh"
+#include "wc_count2.cuh"
 #include "wc_shuffle.cuh"
 #include "wc_sort.cuh"
 #include <cub/cub.cuh>
@@ -109,7 +110,10 @@ struct wc_engine {
     } while (0)
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-namespace { constexpr u32 kMaxParts = 64; }
+namespace {
+constexpr u32 kMaxParts = 64;
+constexpr u32 kMaxTokenWarps = wc::k2Warps > wc::kProducers ? wc::k2Warps : wc::kProducers; // per CTA, over both count kernels
+}
 static int ensure_cursors(wc_engine *e);
 
 // ----------------------------------------------------------------- tables
@@ -223,7 +227,7 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     if (c.long_table_log2 == 0) c.long_table_log2 = 18;
     if (c.arena_bytes == 0) c.arena_bytes = 256ull << 20;
     if (c.short_table_log2 < 10 || c.short_table_log2 > 32 || c.long_table_log2 < 10 || c.long_table_log2 > 34 ||
-        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT) || (c.flags & ~WC_FLAG_STRICT_REF) != 0 || c.mapper > WC_MAP_LOWER_ASCII) {
+        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT) || (c.flags & ~(WC_FLAG_STRICT_REF | WC_FLAG_LANE_SERIAL)) != 0 || c.mapper > WC_MAP_LOWER_ASCII) {
         e->err = "wc_config out of range";
         return WC_ERR_INVALID;
     }
@@ -239,10 +243,12 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     CK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
     CK(cudaFuncSetAttribute(wc::count_kernel<wc::MapIdentity>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::kSmemTotal));
     CK(cudaFuncSetAttribute(wc::count_kernel<wc::MapLowerAscii>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::kSmemTotal));
+    CK(cudaFuncSetAttribute(wc::count_kernel2<wc::MapIdentity>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::k2SmemTotal));
+    CK(cudaFuncSetAttribute(wc::count_kernel2<wc::MapLowerAscii>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::k2SmemTotal));
     CK(cudaMalloc((void **)&e->d_status, sizeof(wc::Status)));
     CK(cudaMallocHost((void **)&e->h_status, sizeof(wc::Status)));
     e->T.st = e->d_status;
-    e->n_ws = (u32)e->grid * wc::kProducers;
+    e->n_ws = (u32)e->grid * kMaxTokenWarps;
     CK(cudaMalloc((void **)&e->d_ws, sizeof(wc::WarpSummary) * e->n_ws));
     e->ovf_cap = 8ull << 20; // 8 Mi records (256 MiB): more words than a 64 MiB chunk can hold
     CK(cudaMalloc((void **)&e->d_ovf, e->ovf_cap * 32));
@@ -460,30 +466,48 @@ static int finish_sorted(wc_engine *e, u64 stop_abs, std::string &blob, std::vec
     return WC_OK;
 }
 
-// The tokenizer/count kernel with the engine's mapper (wc_config.mapper -> a policy of the kernel).
-static void launch_count_kernel(wc_engine *e, const wc::Launch &L) {
-    switch (e->cfg.mapper) {
-    case WC_MAP_LOWER_ASCII:
-        wc::count_kernel<wc::MapLowerAscii><<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
-        break;
-    default:
-        wc::count_kernel<wc::MapIdentity><<<e->grid, wc::kThreads, wc::kSmemTotal, e->stream>>>(L, e->T);
+// Which kernel counts a forward launch: count_kernel (wc_device.cuh), or -- with WC_FLAG_LANE_SERIAL, or
+// WC_KERNEL=k2 in the environment (A/B timing) -- count_kernel2 (wc_count2.cuh) where it applies: the hash
+// path outside strict-ref mode.  Roll-back launches always run count_kernel.
+static bool forward_uses_kernel2(uint32_t flags, bool sort_mode, bool strict) {
+    static const bool env_k2 = [] { const char *k = getenv("WC_KERNEL"); return k && strcmp(k, "k2") == 0; }();
+    return (env_k2 || (flags & WC_FLAG_LANE_SERIAL) != 0) && !sort_mode && !strict;
+}
+
+// One count launch (forward or roll-back) over `n` bytes.  Both kernels split the piece evenly over
+// their tokenizing warps; L.tiles_per_warp is set here for the kernel that runs.  Returns false if the
+// piece is too large for one launch (a CTA's range must fit 32-bit offsets).
+static bool launch_count(cudaStream_t stream, int grid, uint32_t mapper, wc::Launch L, const wc::Tables &T, bool kernel2) {
+    const u64 tiles = (L.n + wc::kTile - 1) / wc::kTile;
+    const u64 per_cta = kernel2 ? wc::k2Warps : wc::kProducers;
+    const u64 warps = (u64)grid * per_cta;
+    const u64 tpw = (tiles + warps - 1) / warps;
+    if (tpw * per_cta * wc::kTile >= 0xFFFFFFF0ull) return false;
+    L.tiles_per_warp = (u32)tpw;
+    if (kernel2) {
+        if (mapper == WC_MAP_LOWER_ASCII)
+            wc::count_kernel2<wc::MapLowerAscii><<<grid, wc::k2Threads, wc::k2SmemTotal, stream>>>(L, T);
+        else
+            wc::count_kernel2<wc::MapIdentity><<<grid, wc::k2Threads, wc::k2SmemTotal, stream>>>(L, T);
+    } else {
+        if (mapper == WC_MAP_LOWER_ASCII)
+            wc::count_kernel<wc::MapLowerAscii><<<grid, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
+        else
+            wc::count_kernel<wc::MapIdentity><<<grid, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
     }
+    return true;
 }
 
 // Launches the forward count of one piece and its roll-back/summary companion on e->stream.
 static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
     if (n == 0) return WC_OK;
-    const u64 tiles = (n + wc::kTile - 1) / wc::kTile;
-    const u64 warps = (u64)e->grid * wc::kProducers;
-    const u64 tpw = (tiles + warps - 1) / warps;
-    if (tpw * wc::kProducers * wc::kTile >= 0xFFFFFFF0ull) { e->err = "piece too large for one launch"; return WC_ERR_TOO_LARGE; }
-    wc::Launch L;
+    const bool strict = (e->cfg.flags & WC_FLAG_STRICT_REF) != 0;
+    const bool k2 = forward_uses_kernel2(e->cfg.flags, e->sort_mode, strict);
+    wc::Launch L{};
     L.buf = dev; L.n = n; L.base = e->cfg.base_offset + e->consumed;
-    L.tiles_per_warp = (u32)tpw; L.last_piece = last_piece; L.negate = 0;
-    L.strict = (e->cfg.flags & WC_FLAG_STRICT_REF) != 0;
-    L.ws = e->d_ws; L.n_ws = e->n_ws;
-    memset(&L.em, 0, sizeof(L.em));
+    L.last_piece = last_piece; L.negate = 0;
+    L.strict = strict;
+    L.ws = e->d_ws; L.n_ws = (u32)e->grid * (k2 ? wc::k2Warps : wc::kProducers); // one summary per tokenizing warp
     if (e->sort_mode) {
         int rc = ensure_emit_capacity(e, n);
         if (rc != WC_OK) return rc;
@@ -497,10 +521,10 @@ static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_pie
         else CK(cudaEventCreate(ev));
     }
     CK(cudaEventRecord(a, e->stream));
-    launch_count_kernel(e, L);
+    if (!launch_count(e->stream, e->grid, e->cfg.mapper, L, e->T, k2)) { e->err = "piece too large for one launch"; return WC_ERR_TOO_LARGE; }
     CK(cudaEventRecord(mid, e->stream));
-    L.negate = 1;
-    launch_count_kernel(e, L);
+    L.negate = 1; // (reads the forward launch's summaries: same L.ws / L.n_ws)
+    if (!launch_count(e->stream, e->grid, e->cfg.mapper, L, e->T, false)) { e->err = "piece too large for one launch"; return WC_ERR_TOO_LARGE; }
     CK(cudaGetLastError());
     CK(cudaEventRecord(b, e->stream));
     e->ev_used.push_back(wc_engine::EvTriple{a, mid, b});
@@ -1373,8 +1397,8 @@ uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts) { return wc::k
 // up once per device with cudaGetSymbolAddress() while that device is current.
 namespace {
 
-constexpr u32 kStaticMaxSMs = 256;    // more than any sm_100 part has
-constexpr u32 kStaticMaxWarps = kStaticMaxSMs * wc::kProducers; // one WarpSummary per tokenizing warp
+constexpr u32 kStaticMaxSMs = 160;    // more than any sm_100 part has (B200: 148)
+constexpr u32 kStaticMaxWarps = kStaticMaxSMs * kMaxTokenWarps; // one WarpSummary per tokenizing warp
 constexpr size_t kStaticStatusBytes = 512;
 constexpr size_t kStaticScratchBytes = kStaticStatusBytes + sizeof(wc::WarpSummary) * kStaticMaxWarps;
 static_assert(sizeof(wc::Status) <= kStaticStatusBytes, "Status must fit its slot");
@@ -1451,13 +1475,16 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
                 rc = static_fail(WC_ERR_CUDA, "cudaDeviceGetAttribute", ce); break;
             }
             if ((ce = cudaFuncSetAttribute(wc::count_kernel<wc::MapIdentity>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)wc::kSmemTotal)) != cudaSuccess) {
+                                           (int)wc::kSmemTotal)) != cudaSuccess ||
+                (ce = cudaFuncSetAttribute(wc::count_kernel2<wc::MapIdentity>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)wc::k2SmemTotal)) != cudaSuccess) {
                 rc = static_fail(WC_ERR_CUDA, "cudaFuncSetAttribute", ce); break;
             }
             sd.scratch = (unsigned char *)addr; sd.num_sms = sms; sd.ready = true;
         }
-        const u32 n_ws = (u32)sd.num_sms * wc::kProducers;
-        if (n_ws > kStaticMaxWarps) {
+        const bool k2 = forward_uses_kernel2(0, false, false);
+        const u32 n_ws = (u32)sd.num_sms * (k2 ? wc::k2Warps : wc::kProducers);
+        if ((u32)sd.num_sms > kStaticMaxSMs) {
             rc = static_fail(WC_ERR_TOO_LARGE, "wc_count_device_static: this GPU has more SMs than the static scratch covers", cudaSuccess);
             break;
         }
@@ -1478,19 +1505,16 @@ extern "C" int wc_count_device_static(int device, const void *dev_text, size_t n
         }
         static_begin_kernel<<<1, 32, 0, stream>>>(st);
         if (n > 0) {
-            const u64 tiles = (n + wc::kTile - 1) / wc::kTile;
-            const u64 warps = (u64)sd.num_sms * wc::kProducers;
-            const u64 tpw = (tiles + warps - 1) / warps;
-            if (tpw * wc::kProducers * wc::kTile >= 0xFFFFFFF0ull) { // a CTA's range must fit 32-bit offsets (as in launch_piece)
+            wc::Launch L{}; // (em.cursor = nullptr: the counting path, not the sort path's record emitter)
+            L.buf = (const uint8_t *)dev_text; L.n = n; L.base = 0;
+            L.last_piece = 1; L.negate = 0; L.strict = 0; L.ws = ws; L.n_ws = n_ws;
+            bool ok = launch_count(stream, sd.num_sms, WC_MAP_IDENTITY, L, T, k2);
+            L.negate = 1;
+            ok = ok && launch_count(stream, sd.num_sms, WC_MAP_IDENTITY, L, T, false);
+            if (!ok) { // a CTA's range must fit 32-bit offsets
                 rc = static_fail(WC_ERR_TOO_LARGE, "wc_count_device_static: text too large for this GPU's SM count", cudaSuccess);
                 break;
             }
-            wc::Launch L{}; // (em.cursor = nullptr: the counting path, not the sort path's record emitter)
-            L.buf = (const uint8_t *)dev_text; L.n = n; L.base = 0; L.tiles_per_warp = (u32)tpw;
-            L.last_piece = 1; L.negate = 0; L.strict = 0; L.ws = ws; L.n_ws = n_ws;
-            wc::count_kernel<wc::MapIdentity><<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
-            L.negate = 1;
-            wc::count_kernel<wc::MapIdentity><<<sd.num_sms, wc::kThreads, wc::kSmemTotal, stream>>>(L, T);
         }
         static_end_kernel<<<1, 32, 0, stream>>>(st, (u64 *)dev_counters);
         if ((ce = cudaGetLastError()) != cudaSuccess) { rc = static_fail(WC_ERR_CUDA, "kernel launch", ce); break; }

@@ -116,8 +116,8 @@ __global__ void peer_push_kernel(Tables T, PeerArea A, u64 base, u64 bytes, u64 
     for (u64 i0 = (u64)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n_w; i0 += stride) { // warp-uniform trip count
         const u64 i = i0 + lane;
         ulonglong2 k = make_ulonglong2(0, 0);
-        u64 c = 0;
-        if (i < n_w) { k = T.w_keys[i]; c = T.w_counts[i]; }
+        u64 c = 0, finv = 0;
+        if (i < n_w) { k = T.w_keys[i]; c = T.w_counts[i]; finv = T.w_finv[i]; }
         const bool used = k.x != 0 && c != 0;
         const u32 m = __ballot_sync(0xFFFFFFFFu, used);
         if (m == 0) continue;
@@ -127,7 +127,7 @@ __global__ void peer_push_kernel(Tables T, PeerArea A, u64 base, u64 bytes, u64 
         if (used && at < A.cap_words) {
             ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(&A.words[at]); // two 16-byte stores over NVLink
             dst[0] = k;
-            dst[1] = make_ulonglong2(c, ~T.w_finv[i]);
+            dst[1] = make_ulonglong2(c, ~finv);
         }
     }
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n_x; i += stride) {

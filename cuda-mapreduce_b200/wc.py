@@ -10,6 +10,7 @@ MODE_REF = 0
 MODE_EXACT = 1
 PATH_AUTO, PATH_HASH, PATH_SORT = 0, 1, 2
 FLAG_STRICT_REF = 1
+FLAG_LANE_SERIAL = 2
 MAP_IDENTITY, MAP_LOWER_ASCII = 0, 1
 
 
@@ -181,12 +182,12 @@ class Engine:
     """with Engine(mode=...) as e: e.feed(bytes); res = e.finish()"""
 
     def __init__(self, mode=MODE_REF, device=0, chunk_bytes=0, short_table_log2=0, long_table_log2=0,
-                 arena_bytes=0, base_offset=0, path=0, strict_ref=False, mapper=0):
+                 arena_bytes=0, base_offset=0, path=0, strict_ref=False, mapper=0, lane_serial=False):
         L = lib()
         cfg = Config()
         L.wc_config_default(C.byref(cfg))
         cfg.mode, cfg.device, cfg.base_offset, cfg.path = mode, device, base_offset, path
-        cfg.flags = FLAG_STRICT_REF if strict_ref else 0
+        cfg.flags = (FLAG_STRICT_REF if strict_ref else 0) | (FLAG_LANE_SERIAL if lane_serial else 0)
         cfg.mapper = mapper
         if chunk_bytes:
             cfg.chunk_bytes = chunk_bytes

@@ -52,6 +52,13 @@ typedef enum wc_status {
                            81-89), empty words credited to row 0 (main.cu:81,103)  */
 #define WC_MODE_EXACT 1 /* plain equality counts of non-empty words */
 
+/* WC_FLAG_LANE_SERIAL (wc_config.flags): count forward launches of the hash path with the alternative
+ * tokenizer kernel count_kernel2 (csrc/wc_count2.cuh: every warp tokenizes, no consumer warps; words that
+ * miss the CTA's table are listed per tile and settled 32 at a time).  Same results; on the measured B200
+ * it is slower than the default kernel on config 2 (1.86 ms vs 1.47 ms per 1e9 bytes) -- both end up bound
+ * by shared-memory wavefronts, see DESIGN.md section 7 -- so it is off by default. */
+#define WC_FLAG_LANE_SERIAL 2u
+
 /* Aggregation path (wc_config.path). */
 #define WC_PATH_AUTO 0
 #define WC_PATH_HASH 1 /* shared-memory table spilling to a global open-addressing table */

@@ -121,6 +121,30 @@ def test_fuzz_arbitrary_bytes(eng_ref):
         check_against_oracle(eng_ref, data, what=i)
 
 
+def test_lane_serial_kernel_matches_oracle(pkg, golden):
+    """WC_FLAG_LANE_SERIAL: the alternative forward kernel (count_kernel2) on the golden vectors, on fuzzed
+    text with control bytes, on a tile-straddling long word and on a config-2 / config-5 sample."""
+    from tools.corpus import Corpus
+    rng = random.Random(77)
+    with pkg.Engine(mode=pkg.MODE_REF, chunk_bytes=1 << 20, lane_serial=True, **SMALL) as e:
+        for name, data, _ in golden:
+            if data is not None:
+                check_against_oracle(e, data, what=name)
+        for i in range(120):
+            data = random_text(rng, rng.randint(0, 2500), weird=rng.choice([0.0, 0.05, 0.3]))
+            check_against_oracle(e, data, what=i)
+        check_against_oracle(e, b"ab " + b"x" * 3000 + b" cd\n" + b"y" * 17 + b" " + b"z" * 16 + b"\n", what="long words")
+    for cfg, n, kw in ((2, 24 << 20, dict(short_table_log2=18, long_table_log2=14)),
+                       (5, 6_000_000, dict(short_table_log2=20, long_table_log2=21, arena_bytes=96 << 20))):
+        data = Corpus(cfg, total_bytes=n).bytes()
+        exp = O.fast_mt(data)
+        with pkg.Engine(chunk_bytes=8 << 20, lane_serial=True, **kw) as e:
+            e.feed(data)
+            got = e.finish()
+        assert got.pairs() == exp.pairs() and got.total == exp.total and got.stats["n_flush"] == exp.n_flush
+        assert got.firsts == [f for _, _, f in exp.rows]
+
+
 def long_text(rng, n_tokens, weird):
     return random_text(rng, n_tokens, weird)
 

@@ -31,7 +31,7 @@ def decode_tables(short, long_, arena):
     """{word: (count, first_offset)} from the raw device tables (layout: include/wc.h)."""
     out = {}
     s_n, l_n = 1 << S_LOG2, 1 << L_LOG2
-    keys, counts, finv = short[:2 * s_n], short[2 * s_n:3 * s_n], short[3 * s_n:]
+    keys, counts, finv = short[:2 * s_n], short[2 * s_n:3 * s_n], short[3 * s_n:4 * s_n]
     kraw = keys.tobytes()
     for i in np.nonzero(keys[0::2])[0]:
         if counts[i] == 0:
