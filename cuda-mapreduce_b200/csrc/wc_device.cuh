@@ -72,7 +72,7 @@ static_assert(kConsumers >= 1 && kProducers >= 1 && kDrainBatch % 32 == 0 && kDr
 static_assert((kDefRing & (kDefRing - 1)) == 0 && kDefRing >= 4 * kDrainBatch, "ring size");
 
 enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u, kErrRingTimeout = 16u,
-             kErrEmitFull = 32u };
+             kErrEmitFull = 32u, kErrPeer = 64u };
 
 // Device-resident job state (one per engine).
 struct Status {
@@ -90,6 +90,8 @@ struct Status {
     u64 ovf_count;    // records appended to the overflow log (may exceed its capacity: then err is set)
     u32 p0_found;
     u32 err;
+    u64 job_bytes;    // wc_peer_pull_device: the counters above describe the whole job (job_set), of this many bytes
+    u64 job_set;
     u64 dbg[8];       // WC_PROFILE builds: consumer cycles (wait, claim, global), batches; producer ring-full cycles, total
 };
 

@@ -75,6 +75,7 @@ struct wc_engine {
         u64 seq = 0;               // pushes made / pulls made
         u64 *d_cur = nullptr;      // sender: the push kernel's cursors
         wc::PeerHeader *h_hdr = nullptr; // root: pinned copy of the headers
+        wc::PeerJob *d_job = nullptr;    // root: what wc_peer_pull_device's first kernel leaves for the import
     } peer;
     void *d_ord = nullptr;                   // wc_finish: sort keys and cub scratch
     size_t d_ord_cap = 0;
@@ -196,6 +197,7 @@ void wc_destroy(wc_engine *e) {
     if (e->peer.mapped && e->peer.ipc) cudaIpcCloseMemHandle(e->peer.mapped);
     if (e->peer.d_cur) cudaFree(e->peer.d_cur);
     if (e->peer.h_hdr) cudaFreeHost(e->peer.h_hdr);
+    if (e->peer.d_job) cudaFree(e->peer.d_job);
     if (e->d_fin) cudaFree(e->d_fin);
     if (e->d_ord) cudaFree(e->d_ord);
     if (e->d_fz) cudaFree(e->d_fz);
@@ -729,6 +731,11 @@ int wc_finish(wc_engine *e, wc_result **out) {
     const double t_settle = since();
     e->carry.clear();
     const wc::Status st = *e->h_status;
+    if (st.job_set) { e->job_stats_set = true; e->job_bytes = st.job_bytes; } // (wc_peer_pull_device set the job's counters on the device)
+    if (st.err & wc::kErrPeer) {
+        e->err = "peer gather: a sender's push did not arrive, or its tables / landing area overflowed";
+        return WC_ERR_TOO_LARGE;
+    }
     if (st.err) {
         char msg[160];
         snprintf(msg, sizeof(msg), "device tables full (flags 0x%x: words=%llu long=%llu arena=%llu units)", st.err,
@@ -1216,8 +1223,9 @@ static u64 peer_stride(u64 cap_words, u64 cap_long, u64 cap_blob) {
                         align_up(cap_blob, 8), 256);
 }
 
-static wc::PeerArea peer_area(uint8_t *base, const wc_engine::Peer &p, u32 rank) {
-    uint8_t *a = base + (u64)rank * p.stride;
+// The root's block is [PeerCtl][rank 0: area 0, area 1][rank 1: area 0, area 1]...; job `seq` uses area seq & 1.
+static wc::PeerArea peer_area(uint8_t *block, const wc_engine::Peer &p, u32 rank, u64 seq) {
+    uint8_t *a = block + sizeof(wc::PeerCtl) + (2ull * rank + (seq & 1)) * p.stride;
     wc::PeerArea A;
     A.hdr = (wc::PeerHeader *)a;
     A.words = (wc::WordRecord *)(a + sizeof(wc::PeerHeader));
@@ -1236,9 +1244,10 @@ int wc_peer_root_create(wc_engine *e, uint32_t n_ranks, uint32_t root_rank, uint
     p.n_ranks = n_ranks; p.root_rank = root_rank; p.my_rank = root_rank;
     p.cap_words = words_per_rank; p.cap_long = long_per_rank; p.cap_blob = align_up(blob_bytes_per_rank, 8);
     p.stride = peer_stride(p.cap_words, p.cap_long, p.cap_blob);
-    CK(cudaMalloc((void **)&p.area, p.stride * n_ranks));
-    CK(cudaMemset(p.area, 0, p.stride * n_ranks));
+    CK(cudaMalloc((void **)&p.area, sizeof(wc::PeerCtl) + 2 * p.stride * n_ranks));
+    CK(cudaMemset(p.area, 0, sizeof(wc::PeerCtl) + 2 * p.stride * n_ranks));
     CK(cudaMallocHost((void **)&p.h_hdr, sizeof(wc::PeerHeader) * n_ranks));
+    CK(cudaMalloc((void **)&p.d_job, sizeof(wc::PeerJob)));
     if (handle_out) {
         static_assert(sizeof(cudaIpcMemHandle_t) == WC_PEER_HANDLE_BYTES, "handle size");
         cudaIpcMemHandle_t h;
@@ -1303,8 +1312,9 @@ int wc_peer_push(wc_engine *e, void *dev_flag) {
     const wc_engine::Peer &p = e->peer;
     CK(cudaMemsetAsync(p.d_cur, 0, 4 * sizeof(u64), e->stream));
     e->peer.seq++;
-    wc::peer_push_kernel<<<e->num_sms * 2, 256, 0, e->stream>>>(e->T, peer_area(p.mapped, p, p.my_rank), e->cfg.base_offset,
-                                                               e->consumed, e->peer.seq, p.d_cur, (u32 *)dev_flag);
+    wc::peer_push_kernel<<<e->num_sms * 2, 256, 0, e->stream>>>(e->T, peer_area(p.mapped, p, p.my_rank, p.seq),
+                                                               (const wc::PeerCtl *)p.mapped, e->cfg.base_offset, e->consumed,
+                                                               p.seq, p.d_cur, (u32 *)dev_flag);
     CK(cudaGetLastError());
     e->launches += 1;
     return WC_OK;
@@ -1319,8 +1329,8 @@ int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
     if (rc != WC_OK) return rc;
     // one wait for everything the host needs: this engine's counters and every sender's header
     CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
-    CK(cudaMemcpy2DAsync(p.h_hdr, sizeof(wc::PeerHeader), p.area, p.stride, sizeof(wc::PeerHeader), p.n_ranks,
-                         cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpy2DAsync(p.h_hdr, sizeof(wc::PeerHeader), p.area + sizeof(wc::PeerCtl) + (p.seq & 1) * p.stride, 2 * p.stride,
+                         sizeof(wc::PeerHeader), p.n_ranks, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     wc_shard_stats mine;
     if (e->h_status->ovf_count != 0 || e->h_status->err != 0) { // rare: grow the table / replay its overflow log first
@@ -1356,7 +1366,7 @@ int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
         if (r == p.root_rank || dead(shards[r])) continue;
         const wc::PeerHeader &h = p.h_hdr[r];
         if (h.n_words == 0 && h.n_long == 0) continue;
-        const wc::PeerArea A = peer_area(p.area, p, r);
+        const wc::PeerArea A = peer_area(p.area, p, r, p.seq);
         L.w[L.n] = A.words; L.n_w[L.n] = h.n_words;
         L.x[L.n] = A.longs; L.n_x[L.n] = h.n_long;
         L.blob[L.n] = (const uint8_t *)A.blob;
@@ -1369,10 +1379,29 @@ int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
     // the root's counters become the job's (stream ordered; wc_finish reads them after its own sync)
     wc::set_job_counters_kernel<<<1, 1, 0, e->stream>>>(e->d_status, job.n_flush, job.n_empty, job.lost_empty, job.p0, job.stop,
                                                        job.p0_found);
+    wc::peer_done_kernel<<<1, 1, 0, e->stream>>>((wc::PeerCtl *)p.area, p.seq); // the senders may reuse this job's areas
     CK(cudaGetLastError());
-    e->launches += 1;
+    e->launches += 2;
     e->job_stats_set = true; e->job_bytes = job.bytes;
     if (job_out) *job_out = job;
+    return WC_OK;
+}
+
+int wc_peer_pull_device(wc_engine *e) {
+    if (!e || !e->peer.area) return WC_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    wc_engine::Peer &p = e->peer;
+    p.seq++;
+    int rc = wc_end_input(e);
+    if (rc != WC_OK) return rc;
+    uint8_t *area0 = p.area + sizeof(wc::PeerCtl);
+    wc::peer_wait_reduce_kernel<<<1, 64, 0, e->stream>>>(area0, p.stride, p.n_ranks, p.root_rank, p.seq, e->d_status,
+                                                        e->cfg.base_offset, e->consumed, p.d_job);
+    wc::peer_clear_root_kernel<<<e->num_sms, 256, 0, e->stream>>>(p.d_job, (u64 *)e->table_block, e->table_block_bytes / 8, e->d_status);
+    wc::import_areas_dev_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, p.d_job, area0, p.stride, p.seq, p.cap_words, p.cap_long);
+    wc::peer_done_kernel<<<1, 1, 0, e->stream>>>((wc::PeerCtl *)p.area, p.seq);
+    CK(cudaGetLastError());
+    e->launches += 4;
     return WC_OK;
 }
 

@@ -97,7 +97,12 @@ __global__ void rehash_words_kernel(Tables T, const ulonglong2 *old_keys, const 
 // ---- peer gather (one node, NVLink): every non-root GPU writes its table entries straight into a
 // landing area in the ROOT GPU's memory, mapped into its address space through CUDA IPC.  No staging
 // buffer, no size exchange: the stores travel over NVLink while the scan of the table is still going.
-// One area per sending rank: [PeerHeader][word records][long records][blob].
+// The root's block: [PeerCtl] then, per sending rank, TWO areas [PeerHeader][word records][long records][blob]:
+// job k lands in area k & 1, so that a sender that is one job ahead of the root never writes where the
+// root is still reading; a sender that would be two ahead waits for PeerCtl::done_seq (the root stores
+// the number of the last job it has finished importing there).
+struct PeerCtl { u64 done_seq; u64 pad[31]; }; // 256 bytes
+static_assert(sizeof(PeerCtl) == 256, "control block size");
 struct PeerHeader {          // 256 bytes, written last (by the last block of the push kernel)
     u64 n_words, n_long, blob_bytes;
     u64 flags;               // bit 0: an area was too small; bits 8..: the sender's Status.err; bit 1: overflow log not empty
@@ -109,8 +114,17 @@ static_assert(sizeof(PeerHeader) == 256, "header size");
 struct PeerArea { PeerHeader *hdr; WordRecord *words; LongRecord *longs; u64 *blob; u64 cap_words, cap_long, cap_blob_units; };
 
 // cur (local, zeroed): [0] word records, [1] long records, [2] blob bytes, [3] blocks done
-__global__ void peer_push_kernel(Tables T, PeerArea A, u64 base, u64 bytes, u64 seq, u64 *cur, u32 *flag_out) {
+__global__ void peer_push_kernel(Tables T, PeerArea A, const PeerCtl *ctl, u64 base, u64 bytes, u64 seq, u64 *cur,
+                                 u32 *flag_out) {
     const u32 lane = threadIdx.x & 31;
+    // flow control: area seq & 1 was last used by job seq - 2; the root must be done with that one
+    if (seq > 2) {
+        if (threadIdx.x == 0) {
+            const volatile u64 *done = &ctl->done_seq; // in the root GPU's memory
+            for (u32 spins = 0; *done + 2 < seq && spins < (1u << 24); ++spins) __nanosleep(200);
+        }
+        __syncthreads();
+    }
     const u64 n_w = 1ull << T.w_log2, n_x = 1ull << T.x_log2;
     const u64 stride = (u64)gridDim.x * blockDim.x;
     for (u64 i0 = (u64)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n_w; i0 += stride) { // warp-uniform trip count
@@ -196,6 +210,106 @@ __global__ void import_areas_kernel(Tables T, const __grid_constant__ ImportList
         if (made_w) atomicAdd(&T.st->w_entries, (u64)made_w);
         if (made_x) atomicAdd(&T.st->x_entries, (u64)made_x);
     }
+}
+
+// ---- the root's side without a host round trip (wc_peer_pull_device): one small kernel waits until
+// every sender's header of job `seq` has arrived in this GPU's memory, reduces the shard counters the way
+// wc_shard_stats_reduce() does on the host (main.cu:185: a shard at or after the first STOP contributes
+// nothing; main.cu:81,103: empty words count as lost until the job's first non-empty word), installs the
+// job's counters and leaves, in device memory, the list of areas to import.
+struct PeerJob {
+    u32 n_ranks, root_rank, root_dead, failed;
+    u64 n_w[64], n_x[64]; // per rank: records to import (0: nothing, dead shard, or the root itself)
+};
+
+__global__ void peer_wait_reduce_kernel(uint8_t *area0, u64 stride, u32 n_ranks, u32 root_rank, u64 seq, Status *st,
+                                        u64 root_base, u64 root_bytes, PeerJob *job) {
+    __shared__ u32 s_failed;
+    const u32 r = threadIdx.x;
+    if (r == 0) s_failed = 0;
+    __syncthreads();
+    if (r < n_ranks && r != root_rank) {
+        const volatile PeerHeader *h = reinterpret_cast<const volatile PeerHeader *>(area0 + (2ull * r + (seq & 1)) * stride);
+        u32 spins = 0;
+        while (h->seq != seq && ++spins < (1u << 24)) __nanosleep(100);
+        if (h->seq != seq || h->flags != 0) atomicOr(&s_failed, 1u); // never arrived, or the sender overflowed
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (r != 0) return;
+    // the shard counters in input order (the ranks' shards tile the input in rank order)
+    u64 n_flush = 0, n_empty = 0, lost = 0, p0 = ~0ull, stop = ~0ull, bytes = 0;
+    u32 p0_found = 0;
+    job->n_ranks = n_ranks; job->root_rank = root_rank; job->root_dead = 0; job->failed = s_failed;
+    for (u32 i = 0; i < n_ranks; i++) {
+        u64 s_base, s_bytes, s_flush, s_empty, s_lost, s_p0, s_stop, s_nw = 0, s_nx = 0; u32 s_p0f;
+        if (i == root_rank) {
+            s_base = root_base; s_bytes = root_bytes; s_flush = st->n_flush; s_empty = st->n_empty; s_lost = st->lost_empty;
+            s_p0 = st->p0; s_stop = st->stop; s_p0f = st->p0_found;
+        } else {
+            const PeerHeader *h = reinterpret_cast<const PeerHeader *>(area0 + (2ull * i + (seq & 1)) * stride);
+            s_base = h->base; s_bytes = h->bytes; s_flush = h->n_flush; s_empty = h->n_empty; s_lost = h->lost_empty;
+            s_p0 = h->p0; s_stop = h->stop; s_p0f = (u32)h->p0_found; s_nw = h->n_words; s_nx = h->n_long;
+        }
+        bytes += s_bytes;
+        const bool dead = stop != ~0ull; // a shard after the job's STOP (shards come in input order)
+        if (dead && s_bytes > 0) { if (i == root_rank) job->root_dead = 1; s_nw = 0; s_nx = 0; }
+        job->n_w[i] = s_failed ? 0 : s_nw; job->n_x[i] = s_failed ? 0 : s_nx;
+        if (dead) continue;
+        n_flush += s_flush; n_empty += s_empty;
+        if (!p0_found) {
+            if (s_p0f && s_p0 < s_stop) { p0_found = 1; p0 = s_p0; lost += s_lost; }
+            else lost += s_empty;
+        }
+        if (s_stop != ~0ull) stop = s_stop;
+    }
+    st->n_flush = n_flush; st->n_empty = n_empty; st->lost_empty = lost; st->p0 = p0; st->stop = stop; st->p0_found = p0_found;
+    st->job_bytes = bytes; st->job_set = 1;
+    if (s_failed) atomicOr(&st->err, kErrPeer);
+}
+
+// The root's own shard lies after the job's STOP: what it counted does not belong to the job.
+__global__ void peer_clear_root_kernel(const PeerJob *job, u64 *table_block, u64 n_words, Status *st) {
+    if (!job->root_dead) return;
+    for (u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x; i < n_words; i += (u64)gridDim.x * blockDim.x) table_block[i] = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { st->w_entries = 0; st->x_entries = 0; st->arena_used = 1; st->ovf_count = 0; }
+}
+
+__global__ void import_areas_dev_kernel(Tables T, const PeerJob *job, uint8_t *area0, u64 stride, u64 seq, u64 cap_words,
+                                        u64 cap_long) {
+    u32 made_w = 0, made_x = 0;
+    const u64 tid = blockIdx.x * (u64)blockDim.x + threadIdx.x, nthr = (u64)gridDim.x * blockDim.x;
+    for (u32 a = 0; a < job->n_ranks; a++) {
+        const u64 n_w = job->n_w[a], n_x = job->n_x[a];
+        if (n_w == 0 && n_x == 0) continue;
+        const uint8_t *ar = area0 + (2ull * a + (seq & 1)) * stride;
+        const WordRecord *w = reinterpret_cast<const WordRecord *>(ar + sizeof(PeerHeader));
+        const LongRecord *x = reinterpret_cast<const LongRecord *>(ar + sizeof(PeerHeader) + cap_words * sizeof(WordRecord));
+        const uint8_t *blob = ar + sizeof(PeerHeader) + cap_words * sizeof(WordRecord) + cap_long * sizeof(LongRecord);
+        for (u64 i = tid; i < n_w; i += nthr) {
+            const WordRecord r = w[i];
+            if (r.k0 == 0 || r.count == 0) continue;
+            const u32 len = r.k1 ? 8 + key_len8(r.k1) : key_len8(r.k0);
+            made_w += word_insert(T, r.k0, r.k1, len, r.count, r.first);
+        }
+        for (u64 i = tid; i < n_x; i += nthr) {
+            const LongRecord r = x[i];
+            if (r.len == 0 || r.count == 0) continue;
+            made_x += long_insert<MapIdentity>(&T, blob, r.blob_off, r.len, r.count, r.first);
+        }
+    }
+    made_w = __reduce_add_sync(0xFFFFFFFFu, made_w);
+    made_x = __reduce_add_sync(0xFFFFFFFFu, made_x);
+    if ((threadIdx.x & 31) == 0) {
+        if (made_w) atomicAdd(&T.st->w_entries, (u64)made_w);
+        if (made_x) atomicAdd(&T.st->x_entries, (u64)made_x);
+    }
+}
+
+// The root is done with job `seq`: its areas may be written again (read by the senders' push kernels).
+__global__ void peer_done_kernel(PeerCtl *ctl, u64 seq) {
+    ctl->done_seq = seq;
+    __threadfence_system();
 }
 
 // Installs the job-wide counters without touching what the import kernels are updating.

@@ -7,6 +7,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <condition_variable>
 #include <mutex>
 #include <string>
@@ -17,9 +20,14 @@
 
 static void usage() {
     fprintf(stderr,
-            "usage: wordcount [FILE] [--no-echo] [--strict-ref] [--map=identity|lower] [--mode=ref|exact] [--chunk-bytes=N] [--device=N] [--json]\n"
+            "usage: wordcount [FILE] [--no-echo] [--strict-ref] [--map=identity|lower] [--mode=ref|exact] [--chunk-bytes=N]\n"
+            "                 [--device=N] [--gpus=N] [--force-path=hash|sort] [--json]\n"
             "  FILE defaults to test.txt in the current directory, as in the reference.\n"
-            "  --strict-ref: read lines in pieces of 99 bytes like the reference's fgets(szLine, 100) does.\n");
+            "  --strict-ref: read lines in pieces of 99 bytes like the reference's fgets(szLine, 100) does.\n"
+            "  --gpus=N: shard the file by byte range over GPUs 0..N-1 of this node (cuts at line starts), one engine and\n"
+            "            one feeder thread per GPU, tables gathered on GPU 0 over NVLink peer memory; same output.\n"
+            "  --force-path: the aggregation path (default: hash tables, or the sort path when the first piece of the\n"
+            "            input shows mostly distinct words).\n");
 }
 
 // printf("%s", szLine) for every fgets(szLine, 100) chunk, up to and including the one that stops
@@ -94,9 +102,105 @@ static int stream_file(wc_engine *e, FILE *f) {
     return rc;
 }
 
+// ---- --gpus=N: one process drives N GPUs: byte-range shards cut at line starts, one
+// engine per GPU (wc_config.base_offset = where its shard starts, so first-occurrence offsets stay global),
+// the senders' tables stored straight into GPU 0's memory (wc_peer_attach / wc_peer_push), GPU 0 reduces
+// the shard counters, imports and finishes.  No NCCL: all engines live in this process.
+
+// The first line start at or after `want` in the file (or in `mem`), `size` if there is none.
+static uint64_t line_start_at_or_after(int fd, const std::vector<char> *mem, uint64_t want, uint64_t size) {
+    if (want == 0 || want >= size) return want >= size ? size : 0;
+    if (mem) {
+        if ((*mem)[want - 1] == '\n') return want;
+        const char *nl = (const char *)memchr(mem->data() + want, '\n', size - want);
+        return nl ? (uint64_t)(nl - mem->data()) + 1 : size;
+    }
+    char c;
+    if (pread(fd, &c, 1, (off_t)(want - 1)) == 1 && c == '\n') return want;
+    std::vector<char> win(1 << 20);
+    for (uint64_t pos = want; pos < size;) {
+        const ssize_t k = pread(fd, win.data(), win.size(), (off_t)pos);
+        if (k <= 0) break;
+        const char *nl = (const char *)memchr(win.data(), '\n', (size_t)k);
+        if (nl) return pos + (uint64_t)(nl - win.data()) + 1;
+        pos += (uint64_t)k;
+    }
+    return size;
+}
+
+struct ShardJob {
+    wc_engine *e = nullptr;
+    int rc = WC_OK;
+    std::string err;
+};
+
+// Feeds bytes [lo, hi) of the input to engine `e` (from memory, or from the file through two pinned slabs).
+static int feed_range(wc_engine *e, int fd, const std::vector<char> *mem, uint64_t lo, uint64_t hi) {
+    if (mem) return hi > lo ? wc_feed(e, mem->data() + lo, hi - lo) : WC_OK;
+    constexpr size_t kSlab = (size_t)64 << 20;
+    char *slab = nullptr;
+    if (wc_host_alloc((void **)&slab, kSlab) != WC_OK) return WC_ERR_NOMEM;
+    int rc = WC_OK;
+    for (uint64_t pos = lo; pos < hi && rc == WC_OK;) {
+        const size_t want = (size_t)((hi - pos) < kSlab ? (hi - pos) : kSlab);
+        const ssize_t k = pread(fd, slab, want, (off_t)pos);
+        if (k <= 0) { rc = WC_ERR_INVALID; break; }
+        rc = wc_feed(e, slab, (size_t)k);
+        pos += (uint64_t)k;
+    }
+    wc_host_free(slab);
+    return rc;
+}
+
+static int run_multi_gpu(const wc_config &base, int n_gpus, int fd, const std::vector<char> *mem, uint64_t size, wc_result **out,
+                         std::string *err) {
+    std::vector<uint64_t> cut(n_gpus + 1, size);
+    cut[0] = 0;
+    for (int r = 1; r < n_gpus; r++) {
+        const uint64_t want = size / (uint64_t)n_gpus * (uint64_t)r;
+        cut[r] = line_start_at_or_after(fd, mem, want > cut[r - 1] ? want : cut[r - 1], size);
+    }
+    std::vector<ShardJob> job(n_gpus);
+    int rc = WC_OK;
+    for (int r = 0; r < n_gpus && rc == WC_OK; r++) { // engines first (the senders attach to the root's landing areas)
+        wc_config cfg = base;
+        cfg.device = r;
+        cfg.base_offset = cut[r];
+        rc = wc_create(&job[r].e, &cfg);
+        if (rc != WC_OK) { *err = wc_last_error(nullptr); break; }
+        if (r == 0)
+            rc = wc_peer_root_create(job[0].e, (uint32_t)n_gpus, 0, 1ull << cfg.short_table_log2, 1ull << cfg.long_table_log2,
+                                     cfg.arena_bytes, nullptr);
+        else rc = wc_peer_attach(job[r].e, (uint32_t)r, job[0].e);
+        if (rc != WC_OK) *err = wc_last_error(job[r].e);
+    }
+    if (rc == WC_OK) {
+        std::vector<std::thread> th;
+        for (int r = 0; r < n_gpus; r++)
+            th.emplace_back([&, r] { // one feeder per GPU; a sender pushes its table as soon as its shard is counted
+                ShardJob &j = job[r];
+                j.rc = feed_range(j.e, fd, mem, cut[r], cut[r + 1]);
+                if (j.rc == WC_OK && r != 0) j.rc = wc_peer_push(j.e, nullptr);
+                if (j.rc == WC_OK) j.rc = wc_sync(j.e);
+                if (j.rc != WC_OK) j.err = wc_last_error(j.e);
+            });
+        for (auto &t : th) t.join();
+        for (int r = 0; r < n_gpus; r++)
+            if (job[r].rc != WC_OK && rc == WC_OK) { rc = job[r].rc; *err = job[r].err; }
+        if (rc == WC_OK) { // every push has completed (wc_sync above): the root reduces the counters, imports, finishes
+            rc = wc_peer_pull(job[0].e, nullptr);
+            if (rc == WC_OK) rc = wc_finish(job[0].e, out);
+            if (rc != WC_OK) *err = wc_last_error(job[0].e);
+        }
+    }
+    for (int r = n_gpus - 1; r >= 0; r--) wc_destroy(job[r].e); // (senders first: they hold the root's areas)
+    return rc;
+}
+
 int main(int argc, char **argv) {
     const char *path = "test.txt";
     bool echo = true, json = false;
+    int n_gpus = 1;
     wc_config cfg;
     wc_config_default(&cfg);
     for (int i = 1; i < argc; i++) {
@@ -109,6 +213,9 @@ int main(int argc, char **argv) {
         else if (!strncmp(a, "--mode=", 7)) cfg.mode = !strcmp(a + 7, "exact") ? WC_MODE_EXACT : WC_MODE_REF;
         else if (!strncmp(a, "--chunk-bytes=", 14)) cfg.chunk_bytes = strtoull(a + 14, nullptr, 10);
         else if (!strncmp(a, "--device=", 9)) cfg.device = atoi(a + 9);
+        else if (!strncmp(a, "--gpus=", 7)) n_gpus = atoi(a + 7);
+        else if (!strcmp(a, "--force-path=hash")) cfg.path = WC_PATH_HASH;
+        else if (!strcmp(a, "--force-path=sort")) cfg.path = WC_PATH_SORT;
         else if (!strcmp(a, "-h") || !strcmp(a, "--help")) { usage(); return 0; }
         else if (a[0] == '-' && a[1]) { usage(); return 2; }
         else path = a;
@@ -129,12 +236,29 @@ int main(int argc, char **argv) {
 
     wc_engine *e = nullptr;
     wc_result *r = nullptr;
-    int rc = wc_create(&e, &cfg);
-    if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(nullptr)); return 1; }
-    if (present) rc = wc_feed(e, data.data(), data.size());
-    else if (f) { rc = stream_file(e, f); fclose(f); }
-    if (rc == WC_OK) rc = wc_finish(e, &r);
-    if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(e)); wc_destroy(e); return 1; }
+    int rc;
+    if (n_gpus > 1 && (present || f)) { // shard over GPUs 0..N-1 (a missing file is the single-engine empty run below)
+        if (n_gpus > 64 || cfg.path == WC_PATH_SORT) { fprintf(stderr, "wordcount: --gpus needs 2..64 GPUs and the hash path\n"); return 2; }
+        std::string err;
+        uint64_t size = data.size();
+        int fd = -1;
+        if (!present) {
+            fd = fileno(f);
+            struct stat st;
+            if (fstat(fd, &st) != 0) { fprintf(stderr, "wordcount: cannot stat %s\n", path); return 1; }
+            size = (uint64_t)st.st_size;
+        }
+        rc = run_multi_gpu(cfg, n_gpus, fd, present ? &data : nullptr, size, &r, &err);
+        if (f) fclose(f);
+        if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), err.c_str()); return 1; }
+    } else {
+        rc = wc_create(&e, &cfg);
+        if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(nullptr)); return 1; }
+        if (present) rc = wc_feed(e, data.data(), data.size());
+        else if (f) { rc = stream_file(e, f); fclose(f); }
+        if (rc == WC_OK) rc = wc_finish(e, &r);
+        if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(e)); wc_destroy(e); return 1; }
+    }
     const size_t need = wc_result_render(r, nullptr, 0);
     std::string out(need, '\0');
     wc_result_render(r, &out[0], need);
@@ -150,6 +274,6 @@ int main(int argc, char **argv) {
                 (unsigned long long)s.n_spilled, (unsigned long long)s.n_slow_tiles, s.device_ms);
     }
     wc_result_free(r);
-    wc_destroy(e);
+    if (e) wc_destroy(e);
     return 0; // main.cu:221
 }

@@ -185,12 +185,19 @@ def exchange_and_gather(engine, device, root=0, mode="auto"):
 class PeerGather:
     """Single-node gather over NVLink peer memory (include/wc.h, wc_peer_*): set up once per engine,
     then one call per job.  Every non-root rank stores its table entries and shard counters straight
-    into the root GPU's memory with one kernel; a one-word NCCL all-reduce behind that kernel is both
-    the barrier and the "any sender overflowed?" vote; the root then adds what arrived to its tables.
-    If a sender did overflow, all ranks fall back to exchange_and_gather() together."""
+    into the root GPU's memory with one kernel.
 
-    def __init__(self, engine, device, words_per_rank, long_per_rank, blob_bytes_per_rank, root=0):
-        self.engine, self.device, self.root = engine, device, root
+    device_wait=True (the default; every rank must have a GPU of its own): nothing else happens on the
+    senders, and the root queues a kernel that waits for the senders' headers in its own memory,
+    reduces the shard counters there and imports what arrived -- no collective and no host wait in
+    the job.  A sender that overflowed makes the root's wc_finish fail with WC_ERR_TOO_LARGE.
+
+    device_wait=False: a one-word NCCL all-reduce behind the push is both the barrier and the "any
+    sender overflowed?" vote, the root then waits on the host for the headers; if a sender did
+    overflow, all ranks fall back to exchange_and_gather() together."""
+
+    def __init__(self, engine, device, words_per_rank, long_per_rank, blob_bytes_per_rank, root=0, device_wait=True):
+        self.engine, self.device, self.root, self.device_wait = engine, device, root, device_wait
         world, rank = dist.get_world_size(), dist.get_rank()
         caps = (words_per_rank, long_per_rank, blob_bytes_per_rank)
         handle = torch.zeros(64, dtype=torch.uint8, device=device)
@@ -218,6 +225,12 @@ class PeerGather:
         rank = dist.get_rank()
         if not self.available:
             return exchange_and_gather(self.engine, self.device, self.root)
+        if self.device_wait:
+            if rank != self.root:
+                self.engine.peer_push(None)
+            else:
+                self.engine.peer_pull_device()
+            return None, rank == self.root
         self.flag.zero_()
         if rank != self.root:
             self.engine.peer_push(self.flag.data_ptr())

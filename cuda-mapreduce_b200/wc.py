@@ -130,6 +130,7 @@ def lib():
     L.wc_peer_attach.argtypes = [vp, C.c_uint32, vp]
     L.wc_peer_push.argtypes = [vp, vp]
     L.wc_peer_pull.argtypes = [vp, C.POINTER(ShardStats)]
+    L.wc_peer_pull_device.argtypes = [vp]
     L.wc_key_owner.argtypes = [u64, u64, C.c_uint32]
     L.wc_key_owner.restype = C.c_uint32
     L.wc_count_device_static.argtypes = [C.c_int, vp, sz, vp, C.c_uint32, vp, C.c_uint32, vp, u64, vp, vp]
@@ -285,6 +286,9 @@ class Engine:
 
     def peer_push(self, dev_flag_ptr=None):
         self._ck(lib().wc_peer_push(self.h, C.c_void_p(dev_flag_ptr) if dev_flag_ptr else None))
+
+    def peer_pull_device(self):
+        self._ck(lib().wc_peer_pull_device(self.h))
 
     def peer_pull(self):
         job = ShardStats()

@@ -245,6 +245,16 @@ WC_API int wc_peer_open(wc_engine *e, uint32_t my_rank, uint32_t n_ranks, uint32
 WC_API int wc_peer_attach(wc_engine *e, uint32_t my_rank, wc_engine *root); /* same process */
 WC_API int wc_peer_push(wc_engine *e, void *dev_flag);                      /* asynchronous, on the engine's stream */
 WC_API int wc_peer_pull(wc_engine *root, wc_shard_stats *job_out);
+/* The same without the caller's barrier and without a host round trip, for ranks that each have a GPU of
+ * their own: queues, on the root's stream, a one-block kernel that waits until every sender's header of
+ * this job has arrived in the root GPU's memory and reduces the shard counters there, then the import.
+ * Nothing is returned to the host: the job's counters are in the engine (wc_finish reports them) and a
+ * sender that overflowed, or whose push never arrived, makes wc_finish fail with WC_ERR_TOO_LARGE.
+ * Landing areas are double buffered and a sender two jobs ahead of the root waits for it, so jobs can be
+ * queued back to back with no synchronisation between the ranks at all.  Do NOT use it when a sender
+ * shares the root's GPU (the waiting kernel could then keep the sender's kernel from running): there,
+ * order the push before wc_peer_pull() yourself. */
+WC_API int wc_peer_pull_device(wc_engine *root);
 
 /* ---- wc_count_device_static: counting without any allocation -------------------------------
  *

@@ -103,6 +103,30 @@ def test_real_reference_binary_on_this_gpu(golden):
             assert r.stdout == expect, name
 
 
+REF_LINKED = os.path.join(ROOT, "oracle", "_ref", "main_linked")
+
+
+@pytest.mark.skipif(not os.path.exists(REF_LINKED), reason="oracle/_ref/main_linked not built")
+def test_reference_main_linked_against_libwc(golden):
+    """The drop-in boundary as a binary: the reference's own main()
+    (main.cu:164-222, its splitter and printer untouched) with main.cu:37-162 cut out, linked against
+    libwc.so's runMapReduce (oracle/Makefile, target _ref/main_linked).  Its stdout must be the
+    unmodified reference's, byte for byte."""
+    by = {n: (d, e) for n, d, e in golden}
+    names = ["test_txt", "c2_01_prefix", "c2_02_prefix_order", "c2_03_empty_to_row0", "c2_07_crlf"]
+    names += [n for n in by if n.startswith("c2_") and n not in names][:8]
+    with tempfile.TemporaryDirectory() as td:
+        for name in names:
+            data, expect = by[name]
+            if data is None:
+                continue
+            with open(os.path.join(td, "test.txt"), "wb") as f:
+                f.write(data)
+            r = subprocess.run([REF_LINKED], cwd=td, capture_output=True, timeout=120)
+            assert r.returncode == 0, (name, r.stderr)
+            assert r.stdout == expect, name
+
+
 def test_fuzz_small(eng_ref, eng_exact):
     rng = random.Random(2024)
     for i in range(250):
@@ -408,7 +432,7 @@ def test_peer_gather_three_engines_one_gpu(pkg):
                                  SMALL["arena_bytes"])
         for r in (1, 2):
             engs[r].peer_attach(r, engs[0])
-        for data in texts:
+        for i, data in enumerate(texts + texts[:3]):
             cuts = multi.line_aligned_cuts(data, world)
             for r, e in enumerate(engs):
                 e.reset(base_offset=cuts[r])
@@ -417,14 +441,18 @@ def test_peer_gather_three_engines_one_gpu(pkg):
                 e.peer_push()
             for e in engs[1:]:
                 e.sync()                                   # (stands for the ranks' barrier)
-            job = engs[0].peer_pull()
+            # odd jobs: the root waits for the headers and reduces the shard counters on the device
+            # (wc_peer_pull_device; safe on one GPU here because the pushes have completed)
+            job = engs[0].peer_pull() if i % 2 == 0 else None
+            if job is None:
+                engs[0].peer_pull_device()
             got = engs[0].finish()
             exp = O.fast(data)
             assert got.pairs() == exp.pairs() and got.total == exp.total
             assert got.firsts == [f for _, _, f in exp.rows]
             assert (got.stats["n_flush"], got.stats["n_empty"], got.stats["n_lost_empty"], got.stats["stop"]) == \
                 (exp.n_flush, exp.n_empty, exp.n_lost_empty, exp.stop)
-            assert job.bytes == len(data)
+            assert (job.bytes if job is not None else got.stats["bytes"]) == len(data)
     finally:
         for e in engs:
             e.close()

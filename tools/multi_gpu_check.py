@@ -5,7 +5,9 @@
         --master-port 29533 tools/multi_gpu_check.py [--config 2] [--mb 256]
 
 Every rank counts its shard of a synthetic corpus, the key-owner exchange runs over NCCL, and rank 0
-compares the rows with the oracle on the whole text (bit-exact).  Prints one JSON line per case."""
+compares the rows with the oracle on the whole text (bit-exact).  Prints one JSON line per case
+(exchange: the NCCL direct gather, the NCCL key-owner all-to-all, the NVLink peer gather with the
+device-side wait, and the peer gather with the all-reduce barrier + host wait)."""
 import argparse
 import json
 import os
@@ -42,15 +44,15 @@ def main():
     cases.append(("stop_in_a_later_shard", base[:k] + b"\n" + base[k:]))
     cases.append(("leading_empties_and_long_words", b"  \n" * 1000 + base + b" " + b"q" * 100 + b" " + b"w" * 5000 + b"\n" + base[:9999]))
     ok = True
-    for name, data, mode in [(n, d, m) for (n, d) in cases for m in ("direct", "owner", "peer")]:
+    for name, data, mode in [(n, d, m) for (n, d) in cases for m in ("direct", "owner", "peer", "peer-host")]:
         cuts = multi.line_aligned_cuts(data, world)
         lo, hi = cuts[rank], cuts[rank + 1]
         with pkg.Engine(device=lr, base_offset=lo, short_table_log2=21, long_table_log2=12) as eng:
             eng.feed(data[lo:hi])
             ext = torch.cuda.ExternalStream(eng.stream(), device=dev)
             with torch.cuda.stream(ext):
-                if mode == "peer":
-                    job, is_root = multi.PeerGather(eng, dev, 1 << 21, 1 << 12, 64 << 20).run()
+                if mode.startswith("peer"):  # "peer": the root waits on the device; "peer-host": all-reduce + host wait
+                    job, is_root = multi.PeerGather(eng, dev, 1 << 21, 1 << 12, 64 << 20, device_wait=mode == "peer").run()
                 else:
                     job, is_root = multi.exchange_and_gather(eng, dev, mode=mode)
             if is_root:
