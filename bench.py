@@ -141,6 +141,13 @@ def oracle_digest(config, total, host_view=None):
     from oracle import orc
     from tools.corpus import Corpus
     t0 = time.perf_counter()
+    fixture = os.path.join(ROOT, "tests", "golden", "config%d_full_oracle.json" % config)
+    if os.path.exists(fixture):  # counted ahead of time (tests/golden/make_config_fixtures.py): config 5 takes the oracle minutes
+        fx = json.load(open(fixture))
+        if fx["bytes"] == total:
+            return {"rows": fx["rows"], "total": fx["total"], "n_flush": fx["n_flush"], "stop": fx["stop"], "rows_sha256": None,
+                    "checksum": fx["checksum"], "seconds": None, "threads": None,
+                    "source": "tests/golden/config%d_full_oracle.json" % config}
     if host_view is None:
         try:
             avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
@@ -157,7 +164,8 @@ def oracle_digest(config, total, host_view=None):
     t1 = time.perf_counter()
     keep = config != 5  # (2.9e8 rows there: compare the counters only)
     r = orc.fast_mt(host_view, keep_rows=keep)
-    out = {"rows": r.n_rows, "total": r.total, "n_flush": r.n_flush, "stop": r.stop,
+    out = {"rows": r.n_rows, "total": r.total, "n_flush": r.n_flush, "stop": r.stop, "checksum": r.checksum,
+           "source": "orc_fast_mt on this host, live",
            "rows_sha256": rows_digest(r.rows) if keep else None,
            "seconds": {"generate": round(t1 - t0, 2), "count": round(time.perf_counter() - t1, 2)},
            "threads": os.cpu_count()}
@@ -216,9 +224,9 @@ def ncu_traffic(workload, nbytes):
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_v*_traffic.json")),
                    key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])
     if not files or workload != "config2" or nbytes != 1_000_000_000:
-        return None, None
+        return {}, None
     d = json.load(open(files[-1]))
-    return d["traffic_bytes_per_launch"], "profiles/" + os.path.basename(files[-1])
+    return d, "profiles/" + os.path.basename(files[-1])
 
 
 class Ctx:
@@ -278,7 +286,41 @@ def run_workload(cx, workload, steps, warmup, primary):
     nbytes = hi - lo
     device_corpus = (args.device_corpus and primary) or nbytes > (9 << 29) or not primary
     host = None
-    if device_corpus and wp["config"] != 5:
+    shm = None
+    # (the 100 GB corpus is always run that way when it is a sub-run of the default workload: "sharded across 8 x B200
+    # with streamed host->device chunks" is how BASELINE.json states config 4)
+    want_shm = wp["config"] != 5 and ((args.host_stream and primary) or (workload == "config4" and not primary and not args.no_e2e))
+    if want_shm:  # only if /dev/shm and the host's memory can hold the corpus (decided by the worst rank's view)
+        try:
+            vfs = os.statvfs("/dev/shm")
+            avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+            fits = float(vfs.f_bavail * vfs.f_frsize >= wp["total"] * 1.02 and avail >= wp["total"] * 1.25 + (16 << 30))
+        except Exception:
+            fits = 0.0
+        want_shm = cx.allreduce([fits], "MIN")[0] > 0.5
+    if want_shm:
+        # the corpus sits in HOST memory and is streamed to the GPUs in chunks (BASELINE.json configs[3]): one
+        # shared mapping for all ranks -- every rank generates and pins its own shard of it, and rank 0 later
+        # counts the whole of it with the oracle
+        import numpy as np
+        shm = "/dev/shm/wc_bench_%s_%d.bin" % (workload, wp["total"])
+        if rank == 0:
+            with open(shm, "wb") as f:
+                f.truncate(wp["total"])
+        cx.barrier()
+        whole_map = np.memmap(shm, dtype=np.uint8, mode="r+", shape=(wp["total"],))
+        corpus.fill(whole_map[lo:hi], lo, nbytes, nthreads=max(1, (os.cpu_count() or 1) // world))
+        rt = torch.cuda.cudart()
+        rc_reg = rt.cudaHostRegister(whole_map.ctypes.data + lo, nbytes, 0)
+        shm_pinned = int(rc_reg) == 0  # (if the shard cannot be pinned wc_feed stages it through its own pinned slots)
+        if not shm_pinned:
+            print("bench: cudaHostRegister of the shard failed (%s): feeding pageable memory" % rc_reg, file=sys.stderr)
+        host = torch.from_numpy(whole_map[lo:hi])
+        dev = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+        dev.copy_(host)
+        device_corpus = False
+        no_e2e = args.no_e2e
+    elif device_corpus and wp["config"] != 5:
         # configs 3 / 4: the shard is written by tools/corpus_gpu.cu (byte-identical to the host generator,
         # tests/test_gpu_parity.py); there is no host copy, so no e2e leg
         dev = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
@@ -292,7 +334,7 @@ def run_workload(cx, workload, steps, warmup, primary):
         no_e2e = args.no_e2e or not primary
 
     eng = cx.pkg.Engine(device=local_rank, short_table_log2=wp["s_log2"], long_table_log2=wp["l_log2"], base_offset=lo,
-                        path={"auto": 0, "hash": 1, "sort": 2}[path], strict_ref=args.strict_ref and primary,
+                        path={"auto": 0 if world == 1 else 1, "hash": 1, "sort": 2}[path], strict_ref=args.strict_ref and primary,
                         lane_serial=args.lane_serial)
     ext = torch.cuda.ExternalStream(eng.stream(), device=cx.dev)
     # N > 1: table entries go to rank 0 through NVLink peer memory (wc_peer_*): one push kernel per sender, the
@@ -351,20 +393,21 @@ def run_workload(cx, workload, steps, warmup, primary):
     if rank == 0:
         full = eng.finish(keep_rows=want_rows)
         result_check = {"rows": full.n_rows, "total": full.total, "n_flush": full.stats["n_flush"], "stop": full.stats["stop"],
-                        "path_used": full.stats.get("path_used"),
+                        "path_used": full.stats.get("path_used"), "checksum": full.checksum,
                         "rows_sha256": rows_digest(full.rows) if want_rows else None}
         del full
     cx.barrier()
     if rank == 0 and not args.no_oracle:
-        whole = host.numpy() if (host is not None and world == 1) else None
+        whole = whole_map if shm else (host.numpy() if (host is not None and world == 1) else None)
         od = oracle_digest(wp["config"], wp["total"], whole)
         if isinstance(od, str):
             result_check["oracle_match"] = None
             result_check["oracle_skipped"] = od
         else:
-            result_check["oracle_match"] = all(result_check[k] == od[k] for k in ("rows", "total", "n_flush", "stop", "rows_sha256"))
+            keys = ["rows", "total", "n_flush", "stop", "checksum"] + (["rows_sha256"] if od["rows_sha256"] else [])
+            result_check["oracle_match"] = all(result_check[k] == od[k] for k in keys)
             result_check["oracle_rows_sha256"] = od["rows_sha256"]
-            result_check["oracle"] = {k: od[k] for k in ("rows", "total", "seconds", "threads")}
+            result_check["oracle"] = {k: od[k] for k in ("rows", "total", "checksum", "seconds", "threads", "source")}
     cx.barrier()
     eng.reset()
     eng.count_device(dev.data_ptr(), nbytes, last_piece=(rank == world - 1))
@@ -389,6 +432,13 @@ def run_workload(cx, workload, steps, warmup, primary):
     e2e = None
     if not no_e2e:
         e2e_steps = min(50, max(3, steps // 2))
+        # what the platform gives for the copies alone: every rank's pinned shard -> its GPU, all ranks at once
+        cx.barrier()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            dev.copy_(host, non_blocking=True)
+        torch.cuda.synchronize()
+        h2d_s = cx.allreduce([(time.perf_counter() - t0) / 3], "MAX")[0]
         step_e2e()
         cx.barrier()
         t0 = time.perf_counter()
@@ -399,11 +449,21 @@ def run_workload(cx, workload, steps, warmup, primary):
         e2e_s = cx.allreduce([e2e_s], "MAX")[0]
         cx.barrier()
         e2e = {"value": all_bytes / e2e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": nbytes,
-               "d2h_bytes_per_step": eng.finish_d2h_bytes(), "ms_per_step": e2e_s * 1e3}
+               "d2h_bytes_per_step": eng.finish_d2h_bytes(), "ms_per_step": e2e_s * 1e3,
+               "h2d_ceiling_gbs": all_bytes / h2d_s / 1e9, "frac_of_ceiling": h2d_s / e2e_s,
+               "h2d_ceiling": "plain cudaMemcpyAsync of every rank's pinned shard to its GPU, all ranks at the same time"}
     stats = res.stats
     cx.barrier()  # (the root's landing areas are mapped by the other ranks until they are done)
     gather = None
     eng.close()
+    if shm:
+        if shm_pinned:
+            torch.cuda.cudart().cudaHostUnregister(whole_map.ctypes.data + lo)
+        host = None
+        del whole_map
+        cx.barrier()
+        if rank == 0:
+            os.remove(shm)
     del dev
     torch.cuda.empty_cache()
     if rank != 0:
@@ -423,7 +483,8 @@ def run_workload(cx, workload, steps, warmup, primary):
                    "step": "wc_reset (table memset) + tokenize/count kernel + roll-back/summary kernel"
                            + (" + " + exch if world > 1 else ""),
                    "exchange": exch, "vocab_seed": corpus.vocab_seed, "text_seed": corpus.text_seed},
-        "data": "synthetic" + (" (generated on the device)" if device_corpus else ""),
+        "data": "synthetic" + (" (generated on the device)" if device_corpus else "")
+                + (" (generated into pinned host memory, streamed to the GPUs by wc_feed)" if shm else ""),
         "kernel_ms": kernel_ms, "nbytes": nbytes, "e2e": e2e, "result_check": result_check,
         "gpu_launches": int(launches) * steps, "clocks": clocks,
     }
@@ -446,6 +507,9 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="N > 1: skip the config3 / config4 strong-scaling sub-runs")
     ap.add_argument("--device-corpus", action="store_true",
                     help="generate the corpus straight into device memory (default for shards above 4.5 GiB); no e2e leg")
+    ap.add_argument("--host-stream", action="store_true",
+                    help="keep the corpus in pinned HOST memory (one shared mapping under /dev/shm, a shard per rank) and report "
+                         "e2e: streamed host->device chunks through wc_feed (config 4 as BASELINE.json states it)")
     ap.add_argument("--strict-ref", action="store_true",
                     help="WC_FLAG_STRICT_REF: read lines in 99-byte pieces like the reference's fgets (same results on these corpora)")
     ap.add_argument("--lane-serial", action="store_true", help="WC_FLAG_LANE_SERIAL: the alternative forward kernel (count_kernel2)")
@@ -469,12 +533,15 @@ def main():
                 extras[key] = {"value": sub["value"], "unit": UNIT, "ms_per_step": sub["ms_per_step"], "steps": 10, "warmup": 3,
                                "kernel_ms": sub["kernel_ms"], "bytes_total": sub["nbytes"] * cx.world, "scaling": "strong",
                                "exchange": sub["config"]["exchange"], "oracle_match": sub["result_check"].get("oracle_match"),
+                               "e2e": sub["e2e"],
                                "result_check": sub["result_check"], "data": sub["data"]}
     if cx.rank != 0:
         return
     o = main_out
     peak, peak_src = measured_peak()
-    traffic, traffic_src = ncu_traffic(args.workload, o["nbytes"])
+    ncu, traffic_src = ncu_traffic(args.workload, o["nbytes"])
+    traffic = ncu.get("traffic_bytes_per_launch")
+    winst, wave = ncu.get("warp_instructions_per_launch"), ncu.get("shared_wavefronts_per_launch")
     achieved = o["nbytes"] / (o["kernel_ms"] * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": o["value"], "unit": UNIT, "n_gpus": cx.world, "steps": args.steps, "warmup": args.warmup,
@@ -485,7 +552,10 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "kernel": "wc::count_kernel2 (forward launch)" if args.lane_serial else "wc::count_kernel (forward launch)",
-                     "kernel_ms": o["kernel_ms"], "algorithmic_bytes_per_launch": o["nbytes"]},
+                     "kernel_ms": o["kernel_ms"], "algorithmic_bytes_per_launch": o["nbytes"],
+                     # from the same ncu capture as `traffic`: lane-instructions and shared-memory wavefronts per input byte
+                     "instr_per_byte": (winst * 32 / o["nbytes"]) if winst else None,
+                     "shared_wavefronts_per_word": (wave / o["config"]["words_per_gpu"]) if wave else None},
         "e2e": o["e2e"], "result_check": o["result_check"], "gpu_launches": o["gpu_launches"], "clocks": o["clocks"],
     }
     line.update(extras)

@@ -6,5 +6,5 @@ it contains no computation.  There is no CPU path: every counting call needs the
 B200, and fails loudly otherwise.
 """
 from .wc import (  # noqa: F401
-    FLAG_LANE_SERIAL, FLAG_STRICT_REF, MAP_IDENTITY, MAP_LOWER_ASCII, MODE_EXACT, MODE_REF, PATH_AUTO, PATH_HASH, PATH_SORT, Config, Engine, ShardStats, WcError, build, declared_symbols, lib, lib_path, run_map_reduce,
+    FLAG_LANE_SERIAL, FLAG_STRICT_REF, JOB_LINE_LENGTHS, JOB_WORDCOUNT, MAP_IDENTITY, MAP_LOWER_ASCII, MODE_EXACT, MODE_REF, PATH_AUTO, PATH_HASH, PATH_SORT, Config, Engine, ShardStats, WcError, build, declared_symbols, lib, lib_path, run_map_reduce,
 )

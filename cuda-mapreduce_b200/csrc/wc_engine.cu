@@ -14,6 +14,7 @@
 #include "../../include/wc.h"
 #include "wc_device.cuh"
 #include "wc_count2.cuh"
+#include "wc_jobs.cuh"
 #include "wc_shuffle.cuh"
 #include "wc_sort.cuh"
 #include <cub/cub.cuh>
@@ -54,6 +55,10 @@ struct wc_engine {
 
     // sort path (WC_PATH_SORT): one record per word of 1..16 bytes, sorted and reduced in wc_finish
     bool sort_mode = false;
+    // WC_PATH_AUTO: the path is chosen from the share of distinct words -- of a probe over the head of an
+    // engine's first job, then of every finished job (the next job of the same engine follows it)
+    bool auto_path = false, auto_decided = false;
+    double auto_ratio = -1.0;   // distinct words / words last seen (probe or finished job); < 0: none yet
     wc::EmitBuf em{};           // device buffers; em.cursor is always allocated in sort mode
     u64 em_bound = 0;           // upper bound of records written so far (pieces launched)
     ulonglong2 *so_key = nullptr; u64 *so_count = nullptr, *so_first = nullptr; // wc_aggregate()'s output
@@ -85,6 +90,10 @@ struct wc_engine {
     size_t d_out_cap = 0, h_out_cap = 0;
     bool job_stats_set = false; // wc_shard_stats_set(): the counters describe the whole job, not this shard
     u64 job_bytes = 0;
+
+    // WC_JOB_LINE_LENGTHS (wc_jobs.cuh): histogram bins, the list of lines longer than the bins, its cursor, error flag
+    wc::LineJob line{};
+    void *line_block = nullptr; size_t line_block_bytes = 0;
 
     u64 consumed = 0; // bytes handed to the device so far
     u64 fed = 0;      // bytes given to wc_feed / wc_count_device
@@ -149,6 +158,7 @@ static int reset_device_state(wc_engine *e) {
     *e->h_status = s;
     CK(cudaMemcpyAsync(e->d_status, e->h_status, sizeof(s), cudaMemcpyHostToDevice, e->stream));
     if (e->em.cursor) CK(cudaMemsetAsync(e->em.cursor, 0, sizeof(u64), e->stream));
+    if (e->line_block) CK(cudaMemsetAsync(e->line_block, 0, (wc::kLineBins + 2) * sizeof(u64), e->stream));
     e->em_bound = 0;
     e->so_valid = false;
     return WC_OK;
@@ -187,6 +197,7 @@ void wc_destroy(wc_engine *e) {
         if (e->ev_copied[i]) cudaEventDestroy(e->ev_copied[i]);
         if (e->ev_counted[i]) cudaEventDestroy(e->ev_counted[i]);
     }
+    if (e->line_block) cudaFree(e->line_block);
     if (e->table_block) cudaFree(e->table_block);
     if (e->T.arena) cudaFree(e->T.arena);
     if (e->d_status) cudaFree(e->d_status);
@@ -229,7 +240,7 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     if (c.long_table_log2 == 0) c.long_table_log2 = 18;
     if (c.arena_bytes == 0) c.arena_bytes = 256ull << 20;
     if (c.short_table_log2 < 10 || c.short_table_log2 > 32 || c.long_table_log2 < 10 || c.long_table_log2 > 34 ||
-        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT) || (c.flags & ~(WC_FLAG_STRICT_REF | WC_FLAG_LANE_SERIAL)) != 0 || c.mapper > WC_MAP_LOWER_ASCII) {
+        c.arena_bytes < 4096 || (c.mode != WC_MODE_REF && c.mode != WC_MODE_EXACT) || (c.flags & ~(WC_FLAG_STRICT_REF | WC_FLAG_LANE_SERIAL)) != 0 || c.mapper > WC_MAP_LOWER_ASCII || c.job > WC_JOB_LINE_LENGTHS) {
         e->err = "wc_config out of range";
         return WC_ERR_INVALID;
     }
@@ -258,7 +269,16 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     int rc = alloc_tables(e, c.short_table_log2, c.long_table_log2, c.arena_bytes, &e->T, &e->table_block,
                           &e->table_block_bytes);
     if (rc != WC_OK) return rc;
-    e->sort_mode = c.path == WC_PATH_SORT;
+    if (c.job == WC_JOB_LINE_LENGTHS) { // [bins][cursor, error flag][list of longer lines]
+        const u64 ovf_cap = 1ull << 20;
+        e->line_block_bytes = (wc::kLineBins + 2 + ovf_cap) * sizeof(u64);
+        CK(cudaMalloc(&e->line_block, e->line_block_bytes));
+        u64 *q = (u64 *)e->line_block;
+        e->line.hist = q; e->line.ovf_count = q + wc::kLineBins; e->line.err = (u32 *)(q + wc::kLineBins + 1);
+        e->line.ovf = q + wc::kLineBins + 2; e->line.ovf_cap = ovf_cap;
+    }
+    e->sort_mode = c.path == WC_PATH_SORT && c.job == WC_JOB_WORDCOUNT;
+    e->auto_path = c.path == WC_PATH_AUTO && c.job == WC_JOB_WORDCOUNT;
     if (e->sort_mode) CK(cudaMalloc((void **)&e->em.cursor, sizeof(u64)));
     rc = reset_device_state(e);
     if (rc != WC_OK) return rc;
@@ -288,6 +308,7 @@ int wc_reset(wc_engine *e) {
     int rc = reset_device_state(e);
     if (rc != WC_OK) return rc;
     e->carry.clear();
+    e->auto_decided = false;
     e->job_stats_set = false; e->job_bytes = 0;
     e->consumed = 0; e->fed = 0; e->launches = 0; e->pieces = 0; e->settle_due = false; e->device_ms = 0; e->count_kernel_ms = 0;
     for (auto &p : e->ev_used) { e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.mid); e->ev_pool.push_back(p.b); }
@@ -336,12 +357,16 @@ static int settle_tables(wc_engine *e) {
         if (want == e->T.w_log2 && st.ovf_count == 0) return WC_OK;
         if (want > e->T.w_log2) { int rc = grow_word_table(e, want); if (rc != WC_OK) return rc; }
         if (st.ovf_count) {
+            // The replay may overflow again (then: next round) and appends to the log from its start, so it
+            // reads a copy: records not yet replayed must not be overwritten by the ones it produces.
+            void *copy = nullptr;
+            CK(cudaMallocAsync(&copy, st.ovf_count * sizeof(wc::WordRecord), e->stream));
+            CK(cudaMemcpyAsync(copy, e->d_ovf, st.ovf_count * sizeof(wc::WordRecord), cudaMemcpyDeviceToDevice, e->stream));
             e->h_status->ovf_count = 0;
             CK(cudaMemcpyAsync(&e->d_status->ovf_count, &e->h_status->ovf_count, sizeof(u64), cudaMemcpyHostToDevice, e->stream));
-            // replaying appends to the same log only if the new table overflows again (then: next round);
-            // records are consumed front to back, new ones land behind the ones being read
-            wc::import_words_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, (const wc::WordRecord *)e->d_ovf, st.ovf_count);
+            wc::import_words_kernel<<<e->num_sms * 4, 256, 0, e->stream>>>(e->T, (const wc::WordRecord *)copy, st.ovf_count);
             CK(cudaGetLastError());
+            CK(cudaFreeAsync(copy, e->stream));
         }
     }
     return WC_OK;
@@ -500,9 +525,72 @@ static bool launch_count(cudaStream_t stream, int grid, uint32_t mapper, wc::Lau
     return true;
 }
 
+// ---- WC_PATH_AUTO.  The hash path costs one table update per word but each NEW word costs a 128-bit CAS
+// and, once the vocabulary has outgrown the L2, random DRAM sectors; the sort path costs the same for every
+// word whatever the vocabulary (a 32-byte record written, sorted and read back).  The first job of an engine
+// is probed: the head of its first piece is counted on the hash path, the counters are read, the tables are
+// reset; later jobs follow the ratio of the job before them.  Measured on one B200
+// (profiles/r2_path_crossover.txt) the hash path wins at every share of distinct words that was tried --
+// 0.0003 (config 2: 1.6 ms against 30 ms per GiB) up to 0.80 (config 5 at full size: 55 ms against 125 ms per
+// step) -- so the default threshold is "never" (2.0) and the sort path is taken when the caller asks for it
+// (WC_PATH_SORT: no table to size) or lowers the threshold (WC_AUTO_SORT_RATIO).
+static double auto_sort_ratio() {
+    const char *v = getenv("WC_AUTO_SORT_RATIO");
+    return v ? atof(v) : 2.0;
+}
+constexpr size_t kAutoProbeBytes = (size_t)8 << 20, kAutoProbeMinWords = 100000;
+
+static int set_sort_mode(wc_engine *e, bool on) {
+    if (on && !e->em.cursor) {
+        CK(cudaMalloc((void **)&e->em.cursor, sizeof(u64)));
+        CK(cudaMemsetAsync(e->em.cursor, 0, sizeof(u64), e->stream));
+    }
+    e->sort_mode = on;
+    return WC_OK;
+}
+
+static bool launch_count(cudaStream_t stream, int grid, uint32_t mapper, wc::Launch L, const wc::Tables &T, bool kernel2);
+static int auto_choose_path(wc_engine *e, const uint8_t *dev, size_t n) {
+    if (e->auto_ratio < 0) { // the engine's first job: probe the head of the piece on the hash path
+        e->auto_decided = true;
+        if (n < ((size_t)1 << 20)) return set_sort_mode(e, false);
+        wc::Launch L{};
+        L.buf = dev; L.n = n < kAutoProbeBytes ? n : kAutoProbeBytes; L.base = e->cfg.base_offset; L.ws = e->d_ws;
+        L.n_ws = (u32)e->grid * wc::kProducers;
+        if (!launch_count(e->stream, e->grid, e->cfg.mapper, L, e->T, false)) return WC_ERR_TOO_LARGE;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        const wc::Status st = *e->h_status;
+        const u64 words = st.n_flush - st.n_empty, distinct = st.w_entries + st.x_entries;
+        int rc = reset_device_state(e); // the probe leaves no trace: the job starts from empty tables
+        if (rc != WC_OK) return rc;
+        e->launches += 1;
+        // (a probe that overflowed a small table says nothing: the overflow log counts occurrences, not words)
+        if (words >= kAutoProbeMinWords && st.ovf_count == 0 && st.err == 0) e->auto_ratio = (double)distinct / (double)words;
+    }
+    e->auto_decided = true;
+    return set_sort_mode(e, e->auto_ratio >= auto_sort_ratio());
+}
+
 // Launches the forward count of one piece and its roll-back/summary companion on e->stream.
 static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
     if (n == 0) return WC_OK;
+    if (e->cfg.job == WC_JOB_LINE_LENGTHS) { // the other job: one kernel, its own reducer (wc_jobs.cuh)
+        const int grid = e->num_sms * 2;
+        const u64 tiles = (n + wc::kTile - 1) / wc::kTile, warps = (u64)grid * (wc::kLineThreads / 32);
+        const u64 tpw = (tiles + warps - 1) / warps;
+        if (tpw >= 0xFFFFFFF0ull) { e->err = "piece too large for one launch"; return WC_ERR_TOO_LARGE; }
+        wc::line_length_kernel<<<grid, wc::kLineThreads, 0, e->stream>>>(dev, n, (u32)tpw, last_piece, e->line);
+        CK(cudaGetLastError());
+        e->consumed += n;
+        e->launches += 1;
+        return WC_OK;
+    }
+    if (e->auto_path && !e->auto_decided) { // the first piece of a job
+        int rc = auto_choose_path(e, dev, n);
+        if (rc != WC_OK) return rc;
+    }
     const bool strict = (e->cfg.flags & WC_FLAG_STRICT_REF) != 0;
     const bool k2 = forward_uses_kernel2(e->cfg.flags, e->sort_mode, strict);
     wc::Launch L{};
@@ -714,6 +802,51 @@ int wc_end_input(wc_engine *e) {
     return WC_OK;
 }
 
+// WC_JOB_LINE_LENGTHS: the histogram comes to the host, one row per length that occurs (key in decimal).
+static int finish_line_lengths(wc_engine *e, wc_result **out) {
+    std::vector<u64> bins(wc::kLineBins + 2);
+    CK(cudaMemcpyAsync(bins.data(), e->line_block, bins.size() * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    const u64 n_ovf = bins[wc::kLineBins];
+    if (*(const u32 *)&bins[wc::kLineBins + 1] != 0 || n_ovf > e->line.ovf_cap) {
+        e->err = "line-length job: more lines of 4096+ bytes than its list holds";
+        return WC_ERR_TABLE_FULL;
+    }
+    std::vector<u64> longs((size_t)n_ovf);
+    if (n_ovf) CK(cudaMemcpy(longs.data(), e->line.ovf, n_ovf * sizeof(u64), cudaMemcpyDeviceToHost));
+    std::sort(longs.begin(), longs.end());
+    wc_result *r = new (std::nothrow) wc_result();
+    if (!r) return WC_ERR_NOMEM;
+    auto add = [r](u64 len, u64 count) {
+        char key[24];
+        const int k = snprintf(key, sizeof(key), "%llu", (unsigned long long)len);
+        r->rows.push_back(wc::Row{r->blob.size(), (uint32_t)k, (int64_t)count, len});
+        r->blob.append(key, (size_t)k);
+        r->total += (int64_t)count;
+    };
+    for (u32 len = 0; len < wc::kLineBins; len++)
+        if (bins[len]) add(len, bins[len]);
+    for (size_t i = 0; i < longs.size();) {
+        size_t j = i;
+        while (j < longs.size() && longs[j] == longs[i]) j++;
+        add(longs[i], j - i);
+        i = j;
+    }
+    r->stats.bytes = e->consumed;
+    r->stats.n_flush = (u64)r->total; r->stats.stop = e->consumed; r->stats.n_distinct = r->rows.size();
+    e->finish_d2h = (bins.size() + n_ovf) * sizeof(u64);
+    *out = r;
+    return WC_OK;
+}
+
+// The path this job took, and what it says about the next one (WC_PATH_AUTO).
+static void note_job_path(wc_engine *e, wc_stats *s) {
+    s->path_used = e->sort_mode ? WC_PATH_SORT : WC_PATH_HASH;
+    const u64 words = s->n_flush - s->n_empty;
+    if (words >= kAutoProbeMinWords) e->auto_ratio = (double)s->n_distinct / (double)words;
+    s->distinct_ratio = words ? (double)s->n_distinct / (double)words : 0.0;
+}
+
 int wc_finish(wc_engine *e, wc_result **out) {
     if (!e || !out) return WC_ERR_INVALID;
     *out = nullptr;
@@ -726,6 +859,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
     rc = wc_sync(e);
     if (rc != WC_OK) return rc;
     const double t_sync = since();
+    if (e->cfg.job == WC_JOB_LINE_LENGTHS) return finish_line_lengths(e, out);
     rc = settle_tables(e);
     if (rc != WC_OK) return rc;
     const double t_settle = since();
@@ -945,6 +1079,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
         r->stats.n_distinct = n_valid;
         r->stats.n_long_words = st.n_long; r->stats.n_spilled = st.n_spill; r->stats.n_slow_tiles = st.n_slow_tiles;
         r->stats.table_grows = e->grows; r->stats.device_ms = e->device_ms; r->stats.count_kernel_ms = e->count_kernel_ms;
+        note_job_path(e, &r->stats);
         if (timing)
             fprintf(stderr, "[wc] wc_finish: drain %.2f settle %.2f export+order+reduce+copy %.2f rows %.2f ms (%llu rows of %llu words)\n",
                     t_sync, t_settle - t_sync, t_d2h - t_settle, t_decode - t_d2h, (unsigned long long)n_rows,
@@ -1011,6 +1146,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
     r->stats.table_grows = e->grows;
     r->stats.device_ms = e->device_ms;
     r->stats.count_kernel_ms = e->count_kernel_ms;
+    note_job_path(e, &r->stats);
     wc::finalize_rows(std::move(blob), entries, e->cfg.mode, st.n_empty, lost, r,
                       have_order ? (const uint32_t *)(hfin + off_pk) : nullptr,
                       have_order ? (const uint32_t *)(hfin + off_pf) : nullptr);
@@ -1145,6 +1281,7 @@ int wc_clear_tables(wc_engine *e) {
 int wc_export_counts(wc_engine *e, uint32_t n_parts, uint64_t *word_counts, uint64_t *long_entries,
                      uint64_t *long_blob_bytes) {
     if (!e || !word_counts || n_parts == 0 || n_parts > kMaxParts) return WC_ERR_INVALID;
+    if (e->sort_mode) { e->err = "the key-owner exchange needs the hash path (wc_config.path = WC_PATH_HASH)"; return WC_ERR_INVALID; }
     CK(cudaSetDevice(e->device));
     int rc = ensure_cursors(e);
     if (rc != WC_OK) return rc;
@@ -1239,6 +1376,8 @@ int wc_peer_root_create(wc_engine *e, uint32_t n_ranks, uint32_t root_rank, uint
                         uint64_t blob_bytes_per_rank, void *handle_out) {
     if (!e || n_ranks == 0 || n_ranks > kMaxParts || root_rank >= n_ranks || words_per_rank == 0) return WC_ERR_INVALID;
     if (e->peer.area || e->peer.mapped) { e->err = "peer gather is already set up on this engine"; return WC_ERR_INVALID; }
+    if (e->sort_mode) { e->err = "peer gather needs the hash path"; return WC_ERR_INVALID; }
+    e->auto_path = false; // (the gather moves table entries: the engines of a multi-GPU job stay on the hash path)
     CK(cudaSetDevice(e->device));
     wc_engine::Peer p;
     p.n_ranks = n_ranks; p.root_rank = root_rank; p.my_rank = root_rank;
@@ -1263,6 +1402,8 @@ static int peer_sender_init(wc_engine *e, uint32_t my_rank, uint32_t n_ranks, ui
     if (n_ranks == 0 || n_ranks > kMaxParts || my_rank >= n_ranks || root_rank >= n_ranks || my_rank == root_rank)
         return WC_ERR_INVALID;
     if (e->peer.area || e->peer.mapped) { e->err = "peer gather is already set up on this engine"; return WC_ERR_INVALID; }
+    if (e->sort_mode) { e->err = "peer gather needs the hash path"; return WC_ERR_INVALID; }
+    e->auto_path = false;
     wc_engine::Peer &p = e->peer;
     p.n_ranks = n_ranks; p.root_rank = root_rank; p.my_rank = my_rank;
     p.cap_words = words_per_rank; p.cap_long = long_per_rank; p.cap_blob = align_up(blob_bytes_per_rank, 8);
@@ -1421,7 +1562,7 @@ uint32_t wc_key_owner(uint64_t k0, uint64_t k1, uint32_t n_parts) { return wc::k
 // and every buffer the results are written to.
 //
 // g_static_scratch lives in every GPU's memory from the moment the library is loaded there until
-// the process exits (kStaticScratchBytes, about 121 KiB).  In host code the name `g_static_scratch`
+// the process exits (kStaticScratchBytes, about 106 KiB).  In host code the name `g_static_scratch`
 // is only a handle for the symbol, not a device address, so the address the kernel needs is looked
 // up once per device with cudaGetSymbolAddress() while that device is current.
 namespace {

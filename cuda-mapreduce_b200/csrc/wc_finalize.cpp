@@ -201,6 +201,38 @@ int wc_result_stats(const wc_result *r, wc_stats *out) {
     return WC_OK;
 }
 
+static inline uint64_t mix_u64(uint64_t x) {
+    x ^= x >> 32; x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32; x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
+    return x;
+}
+
+int wc_result_checksum(const wc_result *r, uint64_t out[2]) {
+    if (!r || !out) return WC_ERR_INVALID;
+    const size_t n = r->row_count();
+    const wc::Row *rows = r->row_data();
+    const char *blob = r->blob_data();
+    const unsigned nt = n > (1u << 20) ? std::max(1u, std::min(16u, std::thread::hardware_concurrency())) : 1u;
+    std::vector<uint64_t> a(nt, 0), b(nt, 0);
+    auto work = [&](unsigned t) {
+        uint64_t sa = 0, sb = 0;
+        for (size_t i = n * t / nt; i < n * (t + 1) / nt; i++) {
+            uint64_t h = 0xCBF29CE484222325ull;
+            const unsigned char *w = (const unsigned char *)blob + rows[i].blob_off;
+            for (uint32_t k = 0; k < rows[i].len; k++) { h ^= w[k]; h *= 0x100000001B3ull; }
+            sa += mix_u64(h) * (uint64_t)rows[i].count;
+            sb += mix_u64(h + (uint64_t)i) * (rows[i].first + 1);
+        }
+        a[t] = sa; b[t] = sb;
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nt; t++) th.emplace_back(work, t);
+    work(0);
+    for (auto &x : th) x.join();
+    out[0] = out[1] = 0;
+    for (unsigned t = 0; t < nt; t++) { out[0] += a[t]; out[1] += b[t]; }
+    return WC_OK;
+}
+
 void wc_result_free(wc_result *r) { delete r; }
 
 // main.cu:210-218

@@ -238,7 +238,7 @@ __global__ void peer_wait_reduce_kernel(uint8_t *area0, u64 stride, u32 n_ranks,
     __syncthreads();
     if (r != 0) return;
     // the shard counters in input order (the ranks' shards tile the input in rank order)
-    u64 n_flush = 0, n_empty = 0, lost = 0, p0 = ~0ull, stop = ~0ull, bytes = 0;
+    u64 n_flush = 0, n_empty = 0, lost = 0, p0 = ~0ull, stop = ~0ull, bytes = 0, next_base = 0;
     u32 p0_found = 0;
     job->n_ranks = n_ranks; job->root_rank = root_rank; job->root_dead = 0; job->failed = s_failed;
     for (u32 i = 0; i < n_ranks; i++) {
@@ -251,6 +251,8 @@ __global__ void peer_wait_reduce_kernel(uint8_t *area0, u64 stride, u32 n_ranks,
             s_base = h->base; s_bytes = h->bytes; s_flush = h->n_flush; s_empty = h->n_empty; s_lost = h->lost_empty;
             s_p0 = h->p0; s_stop = h->stop; s_p0f = (u32)h->p0_found; s_nw = h->n_words; s_nx = h->n_long;
         }
+        if (s_base != next_base && i > 0) { atomicOr(&st->err, kErrPeer); } // the ranks' shards must tile the input
+        next_base = s_base + s_bytes;
         bytes += s_bytes;
         const bool dead = stop != ~0ull; // a shard after the job's STOP (shards come in input order)
         if (dead && s_bytes > 0) { if (i == root_rank) job->root_dead = 1; s_nw = 0; s_nx = 0; }

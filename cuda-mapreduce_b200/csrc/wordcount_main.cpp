@@ -166,6 +166,7 @@ static int run_multi_gpu(const wc_config &base, int n_gpus, int fd, const std::v
         wc_config cfg = base;
         cfg.device = r;
         cfg.base_offset = cut[r];
+        cfg.path = WC_PATH_HASH; // (the gather moves table entries)
         rc = wc_create(&job[r].e, &cfg);
         if (rc != WC_OK) { *err = wc_last_error(nullptr); break; }
         if (r == 0)

@@ -11,6 +11,7 @@ MODE_EXACT = 1
 PATH_AUTO, PATH_HASH, PATH_SORT = 0, 1, 2
 FLAG_STRICT_REF = 1
 FLAG_LANE_SERIAL = 2
+JOB_WORDCOUNT, JOB_LINE_LENGTHS = 0, 1
 MAP_IDENTITY, MAP_LOWER_ASCII = 0, 1
 
 
@@ -38,6 +39,7 @@ class Config(C.Structure):
         ("struct_size", C.c_uint32), ("device", C.c_int32), ("mode", C.c_int32), ("path", C.c_int32),
         ("chunk_bytes", C.c_uint64), ("short_table_log2", C.c_uint32), ("long_table_log2", C.c_uint32),
         ("arena_bytes", C.c_uint64), ("base_offset", C.c_uint64), ("flags", C.c_uint32), ("mapper", C.c_uint32),
+        ("job", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 
@@ -46,7 +48,7 @@ class Stats(C.Structure):
         ("bytes", C.c_uint64), ("n_flush", C.c_uint64), ("n_empty", C.c_uint64), ("n_lost_empty", C.c_uint64),
         ("stop", C.c_uint64), ("n_distinct", C.c_uint64), ("n_long_words", C.c_uint64), ("n_spilled", C.c_uint64),
         ("n_slow_tiles", C.c_uint64), ("table_grows", C.c_uint64), ("device_ms", C.c_double),
-        ("count_kernel_ms", C.c_double),
+        ("count_kernel_ms", C.c_double), ("path_used", C.c_uint64), ("distinct_ratio", C.c_double),
     ]
 
 
@@ -95,6 +97,7 @@ def lib():
     L.wc_result_total.argtypes = [vp]
     L.wc_result_total.restype = i64
     L.wc_result_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.wc_result_checksum.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.wc_result_free.argtypes = [vp]
     L.wc_result_free.restype = None
     L.wc_result_render.argtypes = [vp, C.c_char_p, sz]
@@ -162,6 +165,9 @@ class Result:
         st = Stats()
         L.wc_result_stats(handle, C.byref(st))
         self.stats = {k: getattr(st, k) for k, _ in Stats._fields_}
+        ck = (C.c_uint64 * 2)()
+        L.wc_result_checksum(handle, ck)
+        self.checksum = [int(ck[0]), int(ck[1])]
         self.rows, self.firsts = [], []
         if keep_rows:
             need = L.wc_result_render(handle, None, 0)
@@ -183,12 +189,13 @@ class Engine:
     """with Engine(mode=...) as e: e.feed(bytes); res = e.finish()"""
 
     def __init__(self, mode=MODE_REF, device=0, chunk_bytes=0, short_table_log2=0, long_table_log2=0,
-                 arena_bytes=0, base_offset=0, path=0, strict_ref=False, mapper=0, lane_serial=False):
+                 arena_bytes=0, base_offset=0, path=0, strict_ref=False, mapper=0, lane_serial=False, job=0):
         L = lib()
         cfg = Config()
         L.wc_config_default(C.byref(cfg))
         cfg.mode, cfg.device, cfg.base_offset, cfg.path = mode, device, base_offset, path
         cfg.flags = (FLAG_STRICT_REF if strict_ref else 0) | (FLAG_LANE_SERIAL if lane_serial else 0)
+        cfg.job = job
         cfg.mapper = mapper
         if chunk_bytes:
             cfg.chunk_bytes = chunk_bytes

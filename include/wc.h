@@ -60,7 +60,11 @@ typedef enum wc_status {
 #define WC_FLAG_LANE_SERIAL 2u
 
 /* Aggregation path (wc_config.path). */
-#define WC_PATH_AUTO 0
+#define WC_PATH_AUTO 0 /* hash tables, unless most words are distinct: the first job of an engine is probed (the head of
+                          its first piece is counted, the counters read, the tables reset), later jobs follow the ratio
+                          of the job before them; the sort path is taken above WC_AUTO_SORT_RATIO (environment).  Its
+                          default is 2.0 = never: on one B200 the hash path won at every ratio measured, up to 0.80
+                          (profiles/r2_path_crossover.txt).  wc_stats.path_used says which one ran. */
 #define WC_PATH_HASH 1 /* shared-memory table spilling to a global open-addressing table */
 #define WC_PATH_SORT 2 /* radix sort of (hash, offset, length) + segmented reduce */
 
@@ -80,6 +84,19 @@ typedef enum wc_status {
 #define WC_MAP_IDENTITY 0u
 #define WC_MAP_LOWER_ASCII 1u /* 'A'..'Z' counted as 'a'..'z' (a case-insensitive word count) */
 
+/* wc_config.job: which map/reduce pair runs over the input.  The reference's skeleton takes a user mapper()
+ * (main.cu:37) and reducer() (main.cu:69); the word count is the one pair it ships.
+ *   WC_JOB_WORDCOUNT     map: word -> (word, 1); reduce: count per word, merged by main.cu's prefix rule
+ *                        (WC_MODE_REF) or plain equality (WC_MODE_EXACT).  Everything above describes it.
+ *   WC_JOB_LINE_LENGTHS  map: every line (what fgets delivers, main.cu:179; the final one may lack its
+ *                        line feed) -> (its length in bytes without the line feed, 1); reduce: count per
+ *                        length.  Same engine calls (wc_feed / wc_count_device pieces must end at line ends,
+ *                        as for the word count); wc_finish returns one row per length that occurs, the
+ *                        key rendered in decimal, rows in increasing length, total = number of lines.
+ *                        mode, path, mapper and flags do not apply (no STOP rule: every line counts). */
+#define WC_JOB_WORDCOUNT 0u
+#define WC_JOB_LINE_LENGTHS 1u
+
 typedef struct wc_config {
     uint32_t struct_size;      /* = sizeof(wc_config) */
     int32_t device;            /* CUDA device ordinal */
@@ -92,6 +109,8 @@ typedef struct wc_config {
     uint64_t base_offset;      /* offset of this engine's first byte in the whole input (shards) */
     uint32_t flags;            /* WC_FLAG_* */
     uint32_t mapper;           /* WC_MAP_* */
+    uint32_t job;              /* WC_JOB_* */
+    uint32_t reserved;         /* 0 */
 } wc_config;
 
 /* Counters of one finished job; the same numbers the oracle reports. */
@@ -108,6 +127,8 @@ typedef struct wc_stats {
     uint64_t table_grows;    /* times a device table was re-hashed into a larger one */
     double device_ms;        /* device time of this job's kernels (CUDA events on the engine's stream) */
     double count_kernel_ms;  /* of which the tokenizer/count kernel alone */
+    uint64_t path_used;      /* WC_PATH_HASH or WC_PATH_SORT: what wc_config.path = WC_PATH_AUTO chose for this job */
+    double distinct_ratio;   /* distinct words / non-empty words of this job (what WC_PATH_AUTO goes by) */
 } wc_stats;
 
 WC_API void wc_config_default(wc_config *cfg);
@@ -156,6 +177,11 @@ WC_API int wc_result_row(const wc_result *r, size_t i, const char **word, size_t
 WC_API uint64_t wc_result_row_first(const wc_result *r, size_t i); /* offset that flushed its first occurrence */
 WC_API int64_t wc_result_total(const wc_result *r);              /* "Total Count", main.cu:214,218 */
 WC_API int wc_result_stats(const wc_result *r, wc_stats *out);
+/* A digest of all rows for results too large to compare row by row (config 5: 2.9e8 rows):
+ * out[0] = sum over rows i of mix(fnv1a64(word_i)) * count_i, out[1] = sum of mix(fnv1a64(word_i) + i) * (first_i + 1),
+ * both modulo 2^64 -- the first says "the same multiset of (word, count)", the second "in the same order, with
+ * the same first offsets".  The oracle computes the same two numbers (orc_result_checksum). */
+WC_API int wc_result_checksum(const wc_result *r, uint64_t out[2]);
 WC_API void wc_result_free(wc_result *r);
 
 /* Writes what main.cu prints after the echo (main.cu:210-218): separator, rows
@@ -263,7 +289,7 @@ WC_API int wc_peer_pull_device(wc_engine *root);
  * that gave the whole device heap to their own pool, and hot paths where the device-wide stall of
  * cudaMalloc/cudaFree is not acceptable.  It runs the same tokenizer/count kernel as
  * wc_count_device(), but the kernel's working state sits in a fixed array inside the library image
- * (about 121 KiB, resident on every GPU that loads libwc.so until the process exits) and the caller
+ * (about 106 KiB, resident on every GPU that loads libwc.so until the process exits) and the caller
  * provides the text and every result buffer.  The call makes no cudaMalloc/cudaFree and no other
  * allocating call, on the device or on the host.
  *
@@ -282,7 +308,7 @@ WC_API int wc_peer_pull_device(wc_engine *root);
  *   stream            a cudaStream_t (NULL = the default stream); everything is asynchronous on it.
  *
  * The tables are cleared by the call itself, so the results describe this text alone.  Limits:
- * n <= WC_STATIC_MAX_BYTES and a GPU of at most 256 SMs; anything larger is refused with
+ * n <= WC_STATIC_MAX_BYTES and a GPU of at most 160 SMs; anything larger is refused with
  * WC_ERR_TOO_LARGE before any work is queued (wc_static_last_error() says which).
  *
  * The first call on each device looks up the array's device address and raises the kernel's

@@ -61,6 +61,9 @@ def lib():
         L.orc_render_stdout.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.POINTER(Result),
                                         C.c_char_p, C.c_size_t]
         L.orc_render_stdout.restype = C.c_size_t
+        L.orc_result_checksum.argtypes = [u8p, C.POINTER(Result), C.POINTER(C.c_uint64)]
+        L.orc_line_lengths.argtypes = [u8p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]
+        L.orc_line_lengths.restype = C.c_size_t
         _lib = L
     return _lib
 
@@ -69,6 +72,9 @@ class Counted:
     """Python view of an orc_result: rows as [(word_bytes, count, first)], plus the counters."""
 
     def __init__(self, data, res, keep_rows=True):
+        ck = (C.c_uint64 * 2)()
+        lib().orc_result_checksum(_ptr(data)[0], C.byref(res), ck)
+        self.checksum = [int(ck[0]), int(ck[1])]
         self.total = res.total
         self.n_flush = res.n_flush
         self.n_empty = res.n_empty
@@ -138,6 +144,16 @@ def fast_mt(data, mode=MODE_REF, nthreads=0, keep_rows=True):
     out = Counted(data, res, keep_rows)
     lib().orc_free(C.byref(res))
     return out
+
+
+def line_lengths(data):
+    """[(length, count)] in increasing length, and the number of lines (the second job, WC_JOB_LINE_LENGTHS)."""
+    p, n = _ptr(data)
+    nl = C.c_uint64()
+    need = lib().orc_line_lengths(p, n, None, None, 0, C.byref(nl))
+    lens, cnts = (C.c_uint64 * max(need, 1))(), (C.c_uint64 * max(need, 1))()
+    lib().orc_line_lengths(p, n, C.cast(lens, C.c_void_p), C.cast(cnts, C.c_void_p), need, C.byref(nl))
+    return [(lens[i], cnts[i]) for i in range(need)], nl.value
 
 
 def flush_formula(data):

@@ -456,3 +456,53 @@ size_t orc_render_stdout(const uint8_t *data, size_t n, int linecap, int file_pr
     sb_put(&s, num, (size_t)k); /* main.cu:218 */
     return s.len;
 }
+
+/* ---- second job: line lengths (main.cu:179 is the line reader; the cap of 99 bytes per piece is lifted) */
+static int cmp_u64(const void *a, const void *b) {
+    const uint64_t x = *(const uint64_t *)a, y = *(const uint64_t *)b;
+    return x < y ? -1 : x > y;
+}
+
+size_t orc_line_lengths(const uint8_t *data, size_t n, uint64_t *lengths, uint64_t *counts, size_t cap, uint64_t *n_lines) {
+    size_t n_l = 0, alloc = 1024;
+    uint64_t *lens = (uint64_t *)malloc(alloc * sizeof(uint64_t));
+    size_t start = 0;
+    for (size_t i = 0; i <= n; i++) {
+        const int at_end = i == n;
+        if (at_end ? (start < n) : (data[i] == 0x0A)) { /* a line feed ends a line; so does the end of the file */
+            if (n_l == alloc) { alloc *= 2; lens = (uint64_t *)realloc(lens, alloc * sizeof(uint64_t)); }
+            lens[n_l++] = (uint64_t)(i - start);
+            start = i + 1;
+        }
+    }
+    if (n_lines) *n_lines = n_l;
+    qsort(lens, n_l, sizeof(uint64_t), cmp_u64);
+    size_t n_distinct = 0;
+    for (size_t i = 0; i < n_l;) {
+        size_t j = i;
+        while (j < n_l && lens[j] == lens[i]) j++;
+        if (n_distinct < cap) { lengths[n_distinct] = lens[i]; counts[n_distinct] = (uint64_t)(j - i); }
+        n_distinct++;
+        i = j;
+    }
+    free(lens);
+    return n_distinct;
+}
+
+/* ---- digest of a whole result (compared with wc_result_checksum of libwc.so) */
+static uint64_t mix_u64(uint64_t x) {
+    x ^= x >> 32; x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32; x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
+    return x;
+}
+
+void orc_result_checksum(const uint8_t *data, const orc_result *r, uint64_t out[2]) {
+    uint64_t sa = 0, sb = 0;
+    for (size_t i = 0; i < r->n_rows; i++) {
+        uint64_t h = 0xCBF29CE484222325ull;
+        const uint8_t *w = data + r->rows[i].off;
+        for (uint32_t k = 0; k < r->rows[i].len; k++) { h ^= w[k]; h *= 0x100000001B3ull; }
+        sa += mix_u64(h) * (uint64_t)r->rows[i].count;
+        sb += mix_u64(h + (uint64_t)i) * (r->rows[i].first + 1);
+    }
+    out[0] = sa; out[1] = sb;
+}

@@ -69,6 +69,11 @@ int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_resul
 
 void orc_free(orc_result *r);
 
+/* A digest of all rows, for results too large to compare row by row: out[0] = sum over rows i of
+ * mix(fnv1a64(word_i)) * count_i, out[1] = sum of mix(fnv1a64(word_i) + i) * (first_i + 1), modulo 2^64
+ * (libwc.so's wc_result_checksum computes the same two numbers from its rows). */
+void orc_result_checksum(const uint8_t *data, const orc_result *r, uint64_t out[2]);
+
 /* The byte-parallel statement of the splitter: for every byte
  * writes 1 into flush[i] iff byte i emits a word; returns STOP.  Used to test
  * that the formula the GPU kernels implement equals the line-by-line code. */
@@ -82,6 +87,13 @@ uint64_t orc_split_flushes(const uint8_t *data, size_t n, int linecap, uint8_t *
  * needed, if cap is too small). */
 size_t orc_render_stdout(const uint8_t *data, size_t n, int linecap, int file_present,
                          const orc_result *r, char *buf, size_t cap);
+
+/* The second job (WC_JOB_LINE_LENGTHS, include/wc.h): the lines of the input the way main.cu's reader sees
+ * them before its 99-byte cap -- fgets delivers everything up to and including a line feed, and what is
+ * left at the end of the file without one (main.cu:179) -- mapped to their length without the line feed.
+ * Writes at most `cap` (length, count) pairs in increasing length; returns how many distinct lengths
+ * there are.  *n_lines gets the number of lines. */
+size_t orc_line_lengths(const uint8_t *data, size_t n, uint64_t *lengths, uint64_t *counts, size_t cap, uint64_t *n_lines);
 
 #ifdef __cplusplus
 }

@@ -103,6 +103,37 @@ def test_real_reference_binary_on_this_gpu(golden):
             assert r.stdout == expect, name
 
 
+def test_cli_gpus_flag(pkg, golden):
+    """wordcount --gpus=N: one process, one engine per GPU, shards cut at line starts, tables gathered on
+    GPU 0 over peer memory -- stdout must be byte-identical to the single-GPU run (and to the oracle)."""
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    from tools.corpus import Corpus
+    exe = os.path.join(ROOT, "cuda-mapreduce_b200", "wordcount")
+    rng = random.Random(5)
+    body = random_text(rng, 120000, weird=0.0).replace(b"\n\n", b"\n")
+    k = body.index(b"\n", len(body) * 3 // 5) + 1
+    cases = [("test_txt", [d for nm, d, _ in golden if nm == "test_txt"][0], True),
+             ("random", body + b"x" * 40 + b" tail", True),
+             ("stop_in_second_half", body[:k] + b"\n" + body[k:], False),
+             ("config2_32MB", Corpus(2, total_bytes=32 << 20).bytes().tobytes(), False)]
+    with tempfile.TemporaryDirectory() as td:
+        p = os.path.join(td, "test.txt")
+        for name, data, echo in cases:
+            with open(p, "wb") as f:
+                f.write(data)
+            flags = [] if echo else ["--no-echo"]
+            one = subprocess.run([exe, p] + flags, cwd=td, capture_output=True, timeout=300)
+            many = subprocess.run([exe, p, "--gpus=%d" % min(n, 8)] + flags, cwd=td, capture_output=True, timeout=300)
+            assert one.returncode == 0 and many.returncode == 0, (name, one.stderr, many.stderr)
+            assert many.stdout == one.stdout, name
+            exp = O.fast(data, render=True)
+            if echo:
+                assert one.stdout == exp.stdout, name
+
+
 REF_LINKED = os.path.join(ROOT, "oracle", "_ref", "main_linked")
 
 
@@ -314,7 +345,7 @@ def test_config3_sample_zipf_1m(pkg):
 
 def test_config5_sample_adversarial(pkg):
     n = 12_000_000
-    got, exp, _ = corpus_check(pkg, 5, n, dict(chunk_bytes=4 << 20, short_table_log2=21, long_table_log2=22,
+    got, exp, _ = corpus_check(pkg, 5, n, dict(chunk_bytes=4 << 20, short_table_log2=21, long_table_log2=22, path=pkg.PATH_HASH,
                                                arena_bytes=128 << 20), straddle=(4 << 20, 6_000_000))
     assert exp.max_line > 99 and got.stats["n_long_words"] > 500000
 
@@ -629,6 +660,74 @@ def test_word_table_grows_instead_of_overflowing(pkg):
         got = e.finish()
         exp = O.fast(data)
         assert got.pairs() == exp.pairs() and got.total == exp.total and got.stats["table_grows"] >= 1
+
+
+def test_second_job_line_lengths(pkg):
+    """WC_JOB_LINE_LENGTHS: another map/reduce pair through the same engine calls --
+    every line mapped to its length, counted per length -- against its own oracle function: fuzzed text,
+    lines longer than the histogram's bins, no final line feed, ragged wc_feed calls, device-resident input."""
+    import torch
+    from tools.corpus import Corpus
+    rng = random.Random(8)
+    cases = [b"", b"\n", b"a", b"ab\n\nabc\nab\nxyz", b"x" * 5000 + b"\n" + b"y" * 4096 + b"\n\n" + b"z" * 70000,
+             Corpus(2, total_bytes=8 << 20).bytes().tobytes(), Corpus(5, total_bytes=3_000_000).bytes().tobytes()]
+    cases += [random_text(rng, rng.randint(0, 3000), weird=rng.choice([0.0, 0.3])) for _ in range(40)]
+    with pkg.Engine(job=pkg.JOB_LINE_LENGTHS, chunk_bytes=1 << 20, **SMALL) as e:
+        for i, data in enumerate(cases):
+            exp, n_lines = O.line_lengths(data)
+            e.reset()
+            if i % 3 == 0:      # ragged pieces
+                pos = 0
+                while pos < len(data):
+                    k = rng.randint(1, 200000)
+                    e.feed(data[pos:pos + k]); pos += k
+            elif i % 3 == 1 and data:
+                buf = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+                e.count_device(buf.data_ptr(), len(data), last_piece=True)
+            else:
+                e.feed(data)
+            got = e.finish()
+            assert [(int(w), c) for w, c in got.rows] == exp, i
+            assert got.total == n_lines
+
+
+def test_auto_path_switches_on_distinct_ratio(pkg, monkeypatch):
+    """WC_PATH_AUTO: an engine's first job is probed (the head of its first piece is counted on the hash
+    path and the counters read), later jobs follow the ratio of the job before them.  Above the threshold
+    -> the sort path; Zipf text -> the hash tables; either way the oracle's rows.  (The shipped threshold
+    is "never" -- the hash path won every measurement -- so the test lowers it to see the switch.)"""
+    from tools.corpus import Corpus
+    monkeypatch.setenv("WC_AUTO_SORT_RATIO", "0.5")
+    adv = Corpus(5, total_bytes=12_000_000).bytes()
+    zipf = Corpus(2, total_bytes=24 << 20).bytes()
+    exp_adv, exp_zipf = O.fast_mt(adv), O.fast_mt(zipf)
+
+    def same(got, exp):
+        return got.pairs() == exp.pairs() and got.total == exp.total and got.stats["n_flush"] == exp.n_flush
+
+    with pkg.Engine(path=pkg.PATH_AUTO, chunk_bytes=4 << 20, short_table_log2=20, long_table_log2=21,
+                    arena_bytes=128 << 20) as e:
+        e.feed(adv)                       # first job of the engine: probed
+        got = e.finish()
+        assert got.stats["path_used"] == pkg.PATH_SORT and got.stats["distinct_ratio"] > 0.5 and same(got, exp_adv)
+        e.reset()
+        e.feed(zipf)                      # follows the job before it (sort) ...
+        got = e.finish()
+        assert got.stats["path_used"] == pkg.PATH_SORT and got.stats["distinct_ratio"] < 0.1 and same(got, exp_zipf)
+        e.reset()
+        e.feed(zipf)                      # ... whose ratio sends this one back to the hash tables
+        got = e.finish()
+        assert got.stats["path_used"] == pkg.PATH_HASH and same(got, exp_zipf)
+    with pkg.Engine(path=pkg.PATH_AUTO, chunk_bytes=4 << 20, short_table_log2=18, long_table_log2=14) as e:
+        e.feed(zipf)                      # probed: few distinct words
+        got = e.finish()
+        assert got.stats["path_used"] == pkg.PATH_HASH and same(got, exp_zipf)
+        import torch
+        dev = torch.from_numpy(adv).cuda()
+        e.reset()
+        e.count_device(dev.data_ptr(), dev.numel(), last_piece=True)  # (device-resident input goes the same way)
+        got = e.finish()
+        assert got.stats["path_used"] == pkg.PATH_HASH and same(got, exp_adv)  # follows the Zipf job: hash, still exact
 
 
 def test_sort_path_matches_oracle(pkg, golden):

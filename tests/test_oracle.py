@@ -185,3 +185,18 @@ def test_fast_cap_matches_literal_with_the_reference_line_buffer(golden):
         assert a.pairs() == b.pairs() and a.total == b.total, i
         assert (a.n_flush, a.n_empty, a.n_lost_empty, a.stop) == (b.n_flush, b.n_empty, b.n_lost_empty, b.stop), i
 
+
+
+def test_line_lengths_oracle_against_python():
+    """The second job's oracle (orc_line_lengths) against a two-line Python statement of it."""
+    import collections
+    rng = random.Random(12)
+    cases = [b"", b"\n", b"a", b"a\n", b"\n\n", b"ab\n\nabc\nab\nxyz", b"x" * 5000 + b"\n" + b"y" * 4096]
+    cases += [random_text(rng, rng.randint(0, 400), weird=rng.choice([0.0, 0.3])) for _ in range(200)]
+    for data in cases:
+        lines = data.split(b"\n")
+        if lines and lines[-1] == b"":
+            lines.pop()  # (what follows the last line feed is a line only if it is not empty)
+        exp = sorted(collections.Counter(len(l) for l in lines).items())
+        got, n_lines = O.line_lengths(data)
+        assert got == exp and n_lines == len(lines), data

@@ -32,6 +32,12 @@ if out_json:
     rd, wr = num("dram__bytes_read.sum"), num("dram__bytes_write.sum")
     u, v = d["gpu__time_duration.sum"]
     ms = float(v) * {"ms": 1.0, "us": 1e-3, "s": 1e3, "ns": 1e-6}.get(u, 1.0)
+    def plain(k):
+        return float(d[k][1]) if k in d else None
     json.dump({"source": rep.split("/")[-1], "kernel": d.get("Kernel Name", ("", ""))[1], "dram_bytes_read": rd,
-               "dram_bytes_write": wr, "traffic_bytes_per_launch": rd + wr, "time_ms_under_ncu": ms}, open(out_json, "w"), indent=1)
+               "dram_bytes_write": wr, "traffic_bytes_per_launch": rd + wr, "time_ms_under_ncu": ms,
+               "warp_instructions_per_launch": plain("smsp__inst_executed.sum"),
+               "shared_wavefronts_per_launch": plain("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum"),
+               "shared_bank_conflict_wavefronts_per_launch": plain("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"),
+               "sm_cycles_active_avg": plain("sm__cycles_active.avg")}, open(out_json, "w"), indent=1)
     open(out_json, "a").write("\n")
