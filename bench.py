@@ -389,6 +389,16 @@ def run_workload(cx, workload, steps, warmup, primary):
     # the rows, checked against the oracle's count of the same bytes
     result_check = None
     want_rows = wp["config"] != 5  # (2.9e8 rows there; decided the same way on every rank)
+    finish_ms = None
+    for _ in range(2):  # (the first wc_finish of an engine allocates its buffers: time the second)
+        step_device()
+        if rank == 0:
+            eng.sync()
+            t0 = time.perf_counter()
+            full = eng.finish(keep_rows=False)  # the reference's reduce on the device + rows to the host (outside `value`)
+            finish_ms = (time.perf_counter() - t0) * 1e3
+            del full
+        cx.barrier()
     step_device()
     if rank == 0:
         full = eng.finish(keep_rows=want_rows)
@@ -485,7 +495,7 @@ def run_workload(cx, workload, steps, warmup, primary):
                    "exchange": exch, "vocab_seed": corpus.vocab_seed, "text_seed": corpus.text_seed},
         "data": "synthetic" + (" (generated on the device)" if device_corpus else "")
                 + (" (generated into pinned host memory, streamed to the GPUs by wc_feed)" if shm else ""),
-        "kernel_ms": kernel_ms, "nbytes": nbytes, "e2e": e2e, "result_check": result_check,
+        "kernel_ms": kernel_ms, "nbytes": nbytes, "e2e": e2e, "result_check": result_check, "finish_ms": finish_ms,
         "gpu_launches": int(launches) * steps, "clocks": clocks,
     }
     return out, host
@@ -557,6 +567,9 @@ def main():
                      "instr_per_byte": (winst * 32 / o["nbytes"]) if winst else None,
                      "shared_wavefronts_per_word": (wave / o["config"]["words_per_gpu"]) if wave else None},
         "e2e": o["e2e"], "result_check": o["result_check"], "gpu_launches": o["gpu_launches"], "clocks": o["clocks"],
+        # `value` stops where the exact per-word counts are in HBM; the reference's reduce half (prefix merge, row order)
+        # and the rows' way to the host are wc_finish: this many ms on top of a step (it is inside `e2e`)
+        "finish_ms": o["finish_ms"],
     }
     line.update(extras)
     if not args.no_cpu_baseline and cx.world == 1 and host is not None:  # (the CPU baseline is timed at N = 1 only)

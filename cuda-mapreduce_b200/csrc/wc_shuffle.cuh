@@ -288,11 +288,24 @@ __global__ void import_areas_dev_kernel(Tables T, const PeerJob *job, uint8_t *a
         const WordRecord *w = reinterpret_cast<const WordRecord *>(ar + sizeof(PeerHeader));
         const LongRecord *x = reinterpret_cast<const LongRecord *>(ar + sizeof(PeerHeader) + cap_words * sizeof(WordRecord));
         const uint8_t *blob = ar + sizeof(PeerHeader) + cap_words * sizeof(WordRecord) + cap_long * sizeof(LongRecord);
-        for (u64 i = tid; i < n_w; i += nthr) {
-            const WordRecord r = w[i];
-            if (r.k0 == 0 || r.count == 0) continue;
-            const u32 len = r.k1 ? 8 + key_len8(r.k1) : key_len8(r.k0);
-            made_w += word_insert(T, r.k0, r.k1, len, r.count, r.first);
+        // four records per thread and step: their home slots are read before any of them is used (the import is
+        // bound by the latency of those reads, not by arithmetic)
+        for (u64 i0 = tid; i0 < n_w; i0 += 4 * nthr) {
+            WordRecord r[4]; u32 slot[4]; Bucket b[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const u64 i = i0 + (u64)j * nthr;
+                r[j] = i < n_w ? w[i] : WordRecord{0, 0, 0, 0};
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const u32 len = r[j].k1 ? 8 + key_len8(r[j].k1) : key_len8(r[j].k0 | 1);
+                slot[j] = word_home(T, r[j].k0, len);
+                b[j] = load_bucket(T, slot[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (r[j].k0 != 0 && r[j].count != 0) made_w += word_insert_at(T, r[j].k0, r[j].k1, r[j].count, r[j].first, slot[j], b[j]);
         }
         for (u64 i = tid; i < n_x; i += nthr) {
             const LongRecord r = x[i];

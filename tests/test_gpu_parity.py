@@ -103,6 +103,19 @@ def test_real_reference_binary_on_this_gpu(golden):
             assert r.stdout == expect, name
 
 
+def test_cli_force_path(pkg):
+    """wordcount --force-path=hash|sort: the same stdout from either aggregation path."""
+    exe = os.path.join(ROOT, "cuda-mapreduce_b200", "wordcount")
+    rng = random.Random(6)
+    data = random_text(rng, 50000, weird=0.01)
+    with tempfile.TemporaryDirectory() as td:
+        with open(os.path.join(td, "test.txt"), "wb") as f:
+            f.write(data)
+        outs = [subprocess.run([exe] + fl, cwd=td, capture_output=True, timeout=300) for fl in ([], ["--force-path=hash"], ["--force-path=sort"])]
+        assert all(o.returncode == 0 for o in outs), [o.stderr for o in outs]
+        assert outs[0].stdout == outs[1].stdout == outs[2].stdout == O.fast(data, render=True).stdout
+
+
 def test_cli_gpus_flag(pkg, golden):
     """wordcount --gpus=N: one process, one engine per GPU, shards cut at line starts, tables gathered on
     GPU 0 over peer memory -- stdout must be byte-identical to the single-GPU run (and to the oracle)."""
