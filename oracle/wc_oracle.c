@@ -228,13 +228,32 @@ static void fast_emit(void *vctx, uint64_t off, uint32_t len, uint64_t flush_off
     fmap_add(m, k0, k1, off, len, 1, flush_off);
 }
 
+/* Bytewise order of two words (shorter first among a word and its extensions).  The first 16 bytes are
+ * compared through the zero-padded key words the table already holds -- a word never contains 0x00, so
+ * the padding sorts a word before every extension of it -- and the text is only touched for two words
+ * that agree on 16 bytes (at 3e8 distinct words the sort is otherwise one cache miss per comparison). */
 static int cmp_lex(const void *a, const void *b, void *vdata) {
     const uint8_t *d = (const uint8_t *)vdata;
     const fent *x = (const fent *)a, *y = (const fent *)b;
-    uint32_t l = x->len < y->len ? x->len : y->len;
-    int c = memcmp(d + x->off, d + y->off, l);
-    if (c) return c;
+    uint64_t p = __builtin_bswap64(x->k0), q = __builtin_bswap64(y->k0);
+    if (p != q) return p < q ? -1 : 1;
+    p = __builtin_bswap64(x->k1); q = __builtin_bswap64(y->k1);
+    if (p != q) return p < q ? -1 : 1;
+    if (x->len > 16 && y->len > 16) {
+        uint32_t l = (x->len < y->len ? x->len : y->len) - 16;
+        int c = memcmp(d + x->off + 16, d + y->off + 16, l);
+        if (c) return c;
+    }
     return (x->len > y->len) - (x->len < y->len);
+}
+
+/* is word t a prefix of (or equal to) word w? */
+static inline int is_prefix_of(const uint8_t *d, const fent *t, const fent *w) {
+    if (t->len > w->len) return 0;
+    if (t->len <= 8) return (w->k0 & (t->len == 8 ? ~0ull : (1ull << (8 * t->len)) - 1)) == t->k0;
+    if (w->k0 != t->k0) return 0;
+    if (t->len <= 16) return (w->k1 & (t->len == 16 ? ~0ull : (1ull << (8 * (t->len - 8))) - 1)) == t->k1;
+    return w->k1 == t->k1 && memcmp(d + t->off + 16, d + w->off + 16, t->len - 16) == 0;
 }
 
 static int cmp_first(const void *a, const void *b) {
@@ -276,8 +295,7 @@ static void finalize(fmap *m, int mode, orc_result *out) {
     for (size_t i = 0; i <= nd; i++) {
         while (sp > 0) {
             size_t t = stk[sp - 1];
-            int open = i < nd && v[t].len <= v[i].len &&
-                       memcmp(m->data + v[t].off, m->data + v[i].off, v[t].len) == 0;
+            int open = i < nd && is_prefix_of(m->data, &v[t], &v[i]);
             if (open) break;
             owner[t] = best[sp - 1];
             if (sp > 1 && v[best[sp - 1]].first < v[best[sp - 2]].first) best[sp - 2] = best[sp - 1];

@@ -124,6 +124,28 @@ def test_chain_arbitrary_bytes(data):
     check_chain(data)
 
 
+def test_chain_long_words_sharing_prefixes():
+    """The prefix sweep of orc_fast orders and tests words through their first 16 bytes held as two key words and
+    reads the text only past them: words of 1..40 bytes over a two-letter alphabet put every case of that on the
+    table (equal on 8, on 16, on more; a word and its extensions on either side of the 8- and 16-byte edges)."""
+    rng = random.Random(4242)
+    for trial in range(60):
+        stems = [bytes(rng.choice(b"ab") for _ in range(rng.choice([7, 8, 9, 15, 16, 17, 24, 40]))) for _ in range(4)]
+        words = []
+        for _ in range(rng.randint(1, 60)):
+            s = rng.choice(stems)
+            w = s[:rng.randint(1, len(s))]
+            if rng.random() < 0.3:
+                w += bytes(rng.choice(b"abc\xff") for _ in range(rng.randint(1, 4)))
+            words.append(w)
+        lines, i = [], 0
+        while i < len(words):
+            k = rng.randint(1, 5)
+            lines.append(b" ".join(words[i:i + k]))
+            i += k
+        check_chain(b"\n".join(lines) + b"\n")
+
+
 def test_fast_mt_equals_fast():
     rng = random.Random(99)
     for trial in range(6):
