@@ -135,7 +135,10 @@ typedef struct {
     const uint8_t *data;
     size_t n_data;
     fent *e;
-    size_t cap, n; /* cap is a power of two */
+    size_t cap, n; /* cap is a power of two; a key's home slot is the TOP log2(cap) bits of its hash, so that
+                    * walking one table in slot order visits another (of any size) in slot order too: merging the
+                    * per-thread tables and growing are then sequential sweeps, not a pile-up of probe runs */
+    int shift;
     uint64_t n_flush, n_empty, n_lost_empty, p0;
     int seen_nonempty;
 } fmap;
@@ -178,6 +181,7 @@ static inline void load_key(const fmap *m, uint64_t off, uint32_t len, uint64_t 
 static void fmap_init(fmap *m, const uint8_t *data, size_t n_data, size_t cap) {
     memset(m, 0, sizeof(*m));
     m->data = data; m->n_data = n_data; m->cap = cap;
+    m->shift = 64 - __builtin_ctzll((unsigned long long)cap);
     m->e = (fent *)calloc(cap, sizeof(fent));
     m->p0 = UINT64_MAX;
 }
@@ -186,7 +190,7 @@ static void fmap_add(fmap *m, uint64_t k0, uint64_t k1, uint64_t off, uint32_t l
 
 static void fmap_grow(fmap *m) {
     fent *old = m->e; size_t ocap = m->cap;
-    m->cap = ocap * 2; m->n = 0;
+    m->cap = ocap * 2; m->n = 0; m->shift--;
     m->e = (fent *)calloc(m->cap, sizeof(fent));
     for (size_t i = 0; i < ocap; i++)
         if (old[i].used) fmap_add(m, old[i].k0, old[i].k1, old[i].off, old[i].len, old[i].count, old[i].first);
@@ -196,7 +200,7 @@ static void fmap_grow(fmap *m) {
 static void fmap_add(fmap *m, uint64_t k0, uint64_t k1, uint64_t off, uint32_t len, int64_t count, uint64_t first) {
     uint64_t hash = mix_key(k0, k1, len);
     if (len > 16) hash = hash_tail(hash, m->data + off + 16, len - 16);
-    size_t mask = m->cap - 1, i = (size_t)hash & mask;
+    size_t mask = m->cap - 1, i = (size_t)(hash >> m->shift);
     for (;;) {
         fent *e = &m->e[i];
         if (!e->used) {
@@ -261,12 +265,73 @@ static int cmp_first(const void *a, const void *b) {
     return (x->first > y->first) - (x->first < y->first);
 }
 
+/* ---- sorting the large jobs on all threads ------------------------------------------------------------------
+ * A bucket function that is monotone in the sort order cuts the array into ranges that can be sorted
+ * independently: count, scatter into a second array, qsort_r every bucket on its own thread.  Returns the
+ * sorted array (the second one; the first is freed), or the input sorted in place when it is small. */
+typedef uint32_t (*orc_bucket_fn)(const void *elem);
+typedef int (*orc_cmp_fn)(const void *, const void *, void *);
+typedef struct {
+    uint8_t *base; size_t size; const size_t *start; uint32_t nb; volatile uint32_t *next;
+    orc_cmp_fn cmp; void *arg;
+} psort_job;
+
+static void *psort_main(void *vp) {
+    psort_job *j = (psort_job *)vp;
+    for (;;) {
+        uint32_t b = __sync_fetch_and_add(j->next, 1u);
+        if (b >= j->nb) return NULL;
+        size_t n = j->start[b + 1] - j->start[b];
+        if (n > 1) qsort_r(j->base + j->start[b] * j->size, n, j->size, j->cmp, j->arg);
+    }
+}
+
+static void *parallel_sort(void *base, size_t n, size_t size, uint32_t nb, orc_bucket_fn bucket,
+                           orc_cmp_fn cmp, void *arg, int nthreads) {
+    if (nthreads <= 1 || n < (1u << 18)) { qsort_r(base, n, size, cmp, arg); return base; }
+    uint8_t *src = (uint8_t *)base, *dst = (uint8_t *)malloc(n * size);
+    size_t *start = (size_t *)calloc((size_t)nb + 2, sizeof(size_t));
+    if (!dst || !start) { free(dst); free(start); qsort_r(base, n, size, cmp, arg); return base; }
+    for (size_t i = 0; i < n; i++) start[bucket(src + i * size) + 2]++;
+    for (uint32_t b = 0; b < nb; b++) start[b + 2] += start[b + 1]; /* start[b + 1] = where bucket b begins */
+    for (size_t i = 0; i < n; i++) memcpy(dst + start[bucket(src + i * size) + 1]++ * size, src + i * size, size);
+    free(src);                                                      /* now start[b + 1] = where bucket b ends */
+    volatile uint32_t next = 0;
+    psort_job job = {dst, size, start, nb, &next, cmp, arg};
+    pthread_t th[64];
+    if (nthreads > 64) nthreads = 64;
+    int started = 0;
+    for (int t = 0; t < nthreads; t++) started += pthread_create(&th[started], NULL, psort_main, &job) == 0;
+    if (!started) psort_main(&job);
+    for (int t = 0; t < started; t++) pthread_join(th[t], NULL);
+    free(start);
+    return dst;
+}
+
+static uint32_t bucket_lex(const void *e) { /* the word's first two bytes */
+    return (uint32_t)(__builtin_bswap64(((const fent *)e)->k0) >> 48);
+}
+static int g_first_shift; /* set by finalize() before the rows are sorted: first >> shift < 65536 */
+static uint32_t bucket_first(const void *e) { return (uint32_t)(((const orc_row *)e)->first >> g_first_shift); }
+static int cmp_first_r(const void *a, const void *b, void *unused) { (void)unused; return cmp_first(a, b); }
+
+/* ORC_TIMING=1: phase times of the large jobs on stderr */
+static void orc_tick(const char *what) {
+    static struct timespec last;
+    struct timespec now;
+    if (!getenv("ORC_TIMING")) return;
+    clock_gettime(CLOCK_MONOTONIC, &now);
+    if (what) fprintf(stderr, "[orc] %-18s %8.2f s\n", what, (double)(now.tv_sec - last.tv_sec) + 1e-9 * (double)(now.tv_nsec - last.tv_nsec));
+    last = now;
+}
+
 /* Turn a table of exact counts into the rows main.cu would print. */
-static void finalize(fmap *m, int mode, orc_result *out) {
+static void finalize(fmap *m, int mode, int nthreads, orc_result *out) {
     size_t nd = 0;
     fent *v = (fent *)malloc((m->n ? m->n : 1) * sizeof(fent));
     for (size_t i = 0; i < m->cap; i++)
         if (m->e[i].used) v[nd++] = m->e[i];
+    free(m->e); m->e = NULL; /* the large jobs need the room for the sort */
     out->n_flush = m->n_flush; out->n_empty = m->n_empty; out->n_lost_empty = m->n_lost_empty;
     out->rows = NULL; out->n_rows = 0; out->total = 0;
     if (nd == 0) { free(v); return; }
@@ -287,7 +352,9 @@ static void finalize(fmap *m, int mode, orc_result *out) {
      * prefix.  In bytewise order the words having prefix w are a contiguous
      * run that starts at w, so one sweep with a stack of open prefixes gives
      * every run's minimum. */
-    qsort_r(v, nd, sizeof(fent), cmp_lex, (void *)m->data);
+    orc_tick(NULL);
+    v = (fent *)parallel_sort(v, nd, sizeof(fent), 65536, bucket_lex, cmp_lex, (void *)m->data, nthreads);
+    orc_tick("sort by bytes");
     size_t *owner = (size_t *)malloc(nd * sizeof(size_t));
     size_t *stk = (size_t *)malloc(nd * sizeof(size_t));
     size_t *best = (size_t *)malloc(nd * sizeof(size_t)); /* argmin(first) of the open run */
@@ -303,6 +370,7 @@ static void finalize(fmap *m, int mode, orc_result *out) {
         }
         if (i < nd) { stk[sp] = i; best[sp] = i; sp++; }
     }
+    orc_tick("prefix sweep");
     int64_t *acc = (int64_t *)calloc(nd, sizeof(int64_t));
     size_t nrows = 0;
     for (size_t i = 0; i < nd; i++) { acc[owner[i]] += v[i].count; nrows += owner[i] == i; }
@@ -312,7 +380,9 @@ static void finalize(fmap *m, int mode, orc_result *out) {
             orc_row r = {v[i].off, v[i].len, acc[i], v[i].first};
             out->rows[out->n_rows++] = r;
         }
-    qsort(out->rows, out->n_rows, sizeof(orc_row), cmp_first);
+    for (g_first_shift = 0; (m->n_data >> g_first_shift) >= 65536; g_first_shift++) {}
+    out->rows = (orc_row *)parallel_sort(out->rows, out->n_rows, sizeof(orc_row), 65536, bucket_first, cmp_first_r, NULL, nthreads);
+    orc_tick("rows by first");
     /* S13: empty words after the first non-empty one increment row 0 */
     out->rows[0].count += (int64_t)(m->n_empty - m->n_lost_empty);
     for (size_t i = 0; i < out->n_rows; i++) out->total += out->rows[i].count;
@@ -323,7 +393,7 @@ int orc_fast_cap(const uint8_t *data, size_t n, int mode, int linecap, orc_resul
     memset(out, 0, sizeof(*out));
     fmap m; fmap_init(&m, data, n, 1u << 16);
     split(data, n, 0, linecap, fast_emit, &m, out);
-    finalize(&m, mode, out);
+    finalize(&m, mode, 1, out);
     free(m.e);
     return 0;
 }
@@ -370,10 +440,18 @@ int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_resul
         jobs[nj].data = data; jobs[nj].n = n; jobs[nj].lo = prev; jobs[nj].hi = hi;
         prev = hi; nj++;
     }
+    orc_tick(NULL);
     for (int t = 0; t < nj; t++) pthread_create(&th[t], NULL, slice_main, &jobs[t]);
     for (int t = 0; t < nj; t++) pthread_join(th[t], NULL);
+    orc_tick("slices");
 
-    fmap m; fmap_init(&m, data, n, 1u << 16);
+    /* The merged table is sized for every slice's entries before the first goes in: the slices are walked in
+     * slot order = hash order, and a table that was still small would take such a run as one long pile of
+     * collisions at its start (quadratic); at its final size the run lands slot after slot. */
+    size_t want_cap = 1u << 16, n_all = 0;
+    for (int t = 0; t < nj; t++) n_all += jobs[t].m.n;
+    while (want_cap * 7 < (n_all + 1) * 10) want_cap <<= 1;
+    fmap m; fmap_init(&m, data, n, want_cap);
     out->stop = n;
     for (int t = 0; t < nj; t++) {
         slice_job *j = &jobs[t];
@@ -390,9 +468,10 @@ int orc_fast_mt(const uint8_t *data, size_t n, int mode, int nthreads, orc_resul
         if (j->st.max_line > out->max_line) out->max_line = j->st.max_line;
         if (j->st.stop < j->hi) { out->stop = j->st.stop; break; } /* main.cu:185: later slices never ran */
     }
-    finalize(&m, mode, out);
-    free(m.e);
     for (int t = 0; t < nj; t++) free(jobs[t].m.e);
+    orc_tick("merge of slices");
+    finalize(&m, mode, nthreads, out);
+    free(m.e);
     free(jobs); free(th);
     return 0;
 }
