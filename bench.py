@@ -133,7 +133,7 @@ def rows_digest(rows):
     return h.hexdigest()
 
 
-def oracle_digest(config, total, host_view=None):
+def oracle_digest(config, total, host_view=None, live=False):
     """The whole job counted by the oracle (orc_fast_mt, all host threads): the text is regenerated on
     the host from the same seeds (or taken from host_view when the caller already holds all of it).
     Returns a dict, or a reason string if the host cannot hold the text."""
@@ -142,7 +142,7 @@ def oracle_digest(config, total, host_view=None):
     from tools.corpus import Corpus
     t0 = time.perf_counter()
     fixture = os.path.join(ROOT, "tests", "golden", "config%d_full_oracle.json" % config)
-    if os.path.exists(fixture):  # counted ahead of time (tests/golden/make_config_fixtures.py): config 5 takes the oracle minutes
+    if os.path.exists(fixture) and not live:  # counted ahead of time (tests/golden/make_config_fixtures.py): config 5 takes the oracle minutes
         fx = json.load(open(fixture))
         if fx["bytes"] == total:
             return {"rows": fx["rows"], "total": fx["total"], "n_flush": fx["n_flush"], "stop": fx["stop"], "rows_sha256": None,
@@ -409,7 +409,7 @@ def run_workload(cx, workload, steps, warmup, primary):
     cx.barrier()
     if rank == 0 and not args.no_oracle:
         whole = whole_map if shm else (host.numpy() if (host is not None and world == 1) else None)
-        od = oracle_digest(wp["config"], wp["total"], whole)
+        od = oracle_digest(wp["config"], wp["total"], whole, live=args.oracle_live)
         if isinstance(od, str):
             result_check["oracle_match"] = None
             result_check["oracle_skipped"] = od
@@ -513,6 +513,7 @@ def main():
     ap.add_argument("--table-log2", type=int, default=0, help="override the word table size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    ap.add_argument("--oracle-live", action="store_true", help="count the job with the oracle on this host even where tests/golden holds its result (config 5)")
     ap.add_argument("--no-oracle", action="store_true", help="profiling runs: skip the oracle comparison of the result")
     ap.add_argument("--no-extras", action="store_true", help="N > 1: skip the config3 / config4 strong-scaling sub-runs")
     ap.add_argument("--device-corpus", action="store_true",

@@ -23,6 +23,18 @@
 #include <unordered_map>
 #include "wc_finalize.h"
 #include "wc_reduce.cuh"
+#include <nvtx3/nvToolsExt.h> // header-only (v3): a no-op unless a tool (nsys, ncu --nvtx) injects itself
+
+namespace {
+// One NVTX range per ABI call and per phase of wc_finish, so that a timeline shows the job's structure
+// (tracing).  Costs two predictable branches when no tool is attached.
+struct Range {
+    explicit Range(const char *name) { nvtxRangePushA(name); }
+    ~Range() { nvtxRangePop(); }
+    Range(const Range &) = delete;
+    Range &operator=(const Range &) = delete;
+};
+} // namespace
 
 using wc::u32;
 using wc::u64;
@@ -345,6 +357,7 @@ static int grow_word_table(wc_engine *e, u32 new_log2) {
 // overflow log.  Leaves e->h_status up to date.  No word is ever dropped: wc_device.cuh logs what the
 // table could not take.
 static int settle_tables(wc_engine *e) {
+    Range nvtx_range("wc: settle tables");
     for (int round = 0; round < 8; round++) {
         CK(cudaMemcpyAsync(e->h_status, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
@@ -406,6 +419,7 @@ static int ensure_emit_capacity(wc_engine *e, size_t n) {
 // Sort path, device half: sort the records by hash, mark and number the runs of equal words, reduce
 // every run to (word, count, first offset).  The result stays in device memory (e->so_*).
 static int sort_aggregate(wc_engine *e, u64 stop_abs) {
+    Range nvtx_range("wc: sort + segmented reduce");
     if (e->so_valid) return WC_OK;
     if (e->so_key) { cudaFree(e->so_key); cudaFree(e->so_count); cudaFree(e->so_first); e->so_key = nullptr; }
     e->so_runs = 0; e->so_coll = 0;
@@ -575,6 +589,7 @@ static int auto_choose_path(wc_engine *e, const uint8_t *dev, size_t n) {
 
 // Launches the forward count of one piece and its roll-back/summary companion on e->stream.
 static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_piece) {
+    Range nvtx_range("wc: count piece");
     if (n == 0) return WC_OK;
     if (e->cfg.job == WC_JOB_LINE_LENGTHS) { // the other job: one kernel, its own reducer (wc_jobs.cuh)
         const int grid = e->num_sms * 2;
@@ -693,6 +708,7 @@ static int feed_piece(wc_engine *e, const uint8_t *src, size_t n, int last_piece
 extern "C" {
 
 int wc_feed(wc_engine *e, const void *bytes, size_t n) {
+    Range nvtx_range("wc_feed");
     if (!e || (!bytes && n)) return WC_ERR_INVALID;
     if (n == 0) return WC_OK;
     CK(cudaSetDevice(e->device));
@@ -734,6 +750,7 @@ int wc_feed(wc_engine *e, const void *bytes, size_t n) {
 }
 
 int wc_count_device(wc_engine *e, const void *dev_bytes, size_t n, int last_piece) {
+    Range nvtx_range("wc_count_device");
     if (!e || (!dev_bytes && n)) return WC_ERR_INVALID;
     if (!e->carry.empty()) { e->err = "wc_count_device after an unfinished wc_feed line"; return WC_ERR_INVALID; }
     if (((uintptr_t)dev_bytes & 15) != 0) { e->err = "device buffer must be 16-byte aligned"; return WC_ERR_UNALIGNED; }
@@ -848,6 +865,7 @@ static void note_job_path(wc_engine *e, wc_stats *s) {
 }
 
 int wc_finish(wc_engine *e, wc_result **out) {
+    Range nvtx_range("wc_finish");
     if (!e || !out) return WC_ERR_INVALID;
     *out = nullptr;
     CK(cudaSetDevice(e->device));
@@ -1445,6 +1463,7 @@ int wc_peer_attach(wc_engine *e, uint32_t my_rank, wc_engine *root) {
 }
 
 int wc_peer_push(wc_engine *e, void *dev_flag) {
+    Range nvtx_range("wc_peer_push");
     if (!e || !e->peer.mapped) return WC_ERR_INVALID;
     if (e->sort_mode) { e->err = "peer gather needs the hash path"; return WC_ERR_INVALID; }
     CK(cudaSetDevice(e->device));
@@ -1462,6 +1481,7 @@ int wc_peer_push(wc_engine *e, void *dev_flag) {
 }
 
 int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
+    Range nvtx_range("wc_peer_pull");
     if (!e || !e->peer.area) return WC_ERR_INVALID;
     CK(cudaSetDevice(e->device));
     wc_engine::Peer &p = e->peer;
@@ -1529,6 +1549,7 @@ int wc_peer_pull(wc_engine *e, wc_shard_stats *job_out) {
 }
 
 int wc_peer_pull_device(wc_engine *e) {
+    Range nvtx_range("wc_peer_pull_device");
     if (!e || !e->peer.area) return WC_ERR_INVALID;
     CK(cudaSetDevice(e->device));
     wc_engine::Peer &p = e->peer;
