@@ -4,6 +4,7 @@
 // fgets chunk, then prints separator / rows / separator / "Total Count:N" and exits 0 even when the
 // file is missing (main.cu:174).  `wordcount` with no arguments does exactly that, byte for byte;
 // FILE and the options below are additions.
+#include <cerrno>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -21,11 +22,13 @@
 static void usage() {
     fprintf(stderr,
             "usage: wordcount [FILE] [--no-echo] [--strict-ref] [--map=identity|lower] [--mode=ref|exact] [--chunk-bytes=N]\n"
-            "                 [--device=N] [--gpus=N] [--force-path=hash|sort] [--json]\n"
+            "                 [--device=N] [--gpus=N] [--force-path=hash|sort] [--direct-io] [--json]\n"
             "  FILE defaults to test.txt in the current directory, as in the reference.\n"
             "  --strict-ref: read lines in pieces of 99 bytes like the reference's fgets(szLine, 100) does.\n"
             "  --gpus=N: shard the file by byte range over GPUs 0..N-1 of this node (cuts at line starts), one engine and\n"
             "            one feeder thread per GPU, tables gathered on GPU 0 over NVLink peer memory; same output.\n"
+            "  --direct-io: with --no-echo, read the file with O_DIRECT straight into the pinned slabs (no page cache copy);\n"
+            "            falls back to buffered reads where the file system refuses O_DIRECT.\n"
             "  --force-path: the aggregation path (default: hash tables, or the sort path when the first piece of the\n"
             "            input shows mostly distinct words).\n");
 }
@@ -47,13 +50,39 @@ static void echo_input(const std::vector<char> &d, size_t cap) {
     }
 }
 
+// Reads file bytes [pos, pos + want) into `slab` (page aligned, `cap` bytes, a multiple of kIoAlign) and returns
+// where they start inside it through *at.  With O_DIRECT the kernel wants offset, length and address aligned
+// to the device's block size: the read starts at the aligned offset below pos and is rounded up, so up to
+// kIoAlign - 1 bytes in front of *at are not the caller's.  Returns the number of caller bytes (0 at the end
+// of the file, -1 on error); never more than cap - kIoAlign.
+constexpr size_t kIoAlign = 4096;
+static ssize_t read_at(int fd, bool direct, char *slab, size_t cap, uint64_t pos, size_t want, char **at) {
+    const uint64_t pos_al = direct ? pos & ~(uint64_t)(kIoAlign - 1) : pos;
+    const size_t head = (size_t)(pos - pos_al);
+    if (want > cap - kIoAlign) want = cap - kIoAlign;
+    size_t len = head + want;
+    if (direct) len = (len + kIoAlign - 1) & ~(kIoAlign - 1);
+    size_t got = 0;
+    while (got < len) { // (a short read mid-file is legal; with O_DIRECT it still ends on a block edge)
+        const ssize_t k = pread(fd, slab + got, len - got, (off_t)(pos_al + got));
+        if (k < 0) return -1;
+        if (k == 0) break;
+        got += (size_t)k;
+    }
+    *at = slab + head;
+    if (got <= head) return 0;
+    return (ssize_t)(got - head < want ? got - head : want);
+}
+
 // --no-echo: the file never sits in memory as a whole.  A reader thread fills pinned slabs
 // (wc_host_alloc) while the main thread feeds the previous one to the engine, so reading the file,
-// the PCIe copy and the count kernel overlap.  Returns a wc_status.
-static int stream_file(wc_engine *e, FILE *f) {
+// the PCIe copy and the count kernel overlap; with --direct-io the reads bypass
+// the page cache (O_DIRECT into the pinned slab: one copy, storage -> pinned memory -> GPU).  Returns a wc_status.
+static int stream_file(wc_engine *e, int fd, bool direct) {
     constexpr size_t kSlab = (size_t)64 << 20;
     constexpr int kSlabs = 3;
     char *slab[kSlabs] = {nullptr, nullptr, nullptr};
+    char *at[kSlabs] = {nullptr, nullptr, nullptr};
     size_t fill[kSlabs] = {0, 0, 0};
     for (int i = 0; i < kSlabs; i++)
         if (wc_host_alloc((void **)&slab[i], kSlab) != WC_OK) {
@@ -63,8 +92,9 @@ static int stream_file(wc_engine *e, FILE *f) {
     std::mutex mu;
     std::condition_variable cv;
     int produced = 0, consumed = 0; // slabs filled / slabs fed
-    bool eof = false;
+    bool eof = false, io_error = false;
     std::thread reader([&] {
+        uint64_t pos = 0;
         for (;;) {
             int s;
             {
@@ -72,13 +102,13 @@ static int stream_file(wc_engine *e, FILE *f) {
                 cv.wait(lk, [&] { return produced - consumed < kSlabs; });
                 s = produced % kSlabs;
             }
-            const size_t k = fread(slab[s], 1, kSlab, f);
+            const ssize_t k = read_at(fd, direct, slab[s], kSlab, pos, kSlab, &at[s]);
             {
                 std::lock_guard<std::mutex> lk(mu);
-                if (k == 0) eof = true; else { fill[s] = k; produced++; }
+                if (k <= 0) { eof = true; io_error = k < 0; } else { fill[s] = (size_t)k; produced++; pos += (uint64_t)k; }
             }
             cv.notify_all();
-            if (k == 0) return;
+            if (k <= 0) return;
         }
     });
     int rc = WC_OK;
@@ -90,7 +120,7 @@ static int stream_file(wc_engine *e, FILE *f) {
             if (produced == consumed) break;
             s = consumed % kSlabs;
         }
-        if (rc == WC_OK) rc = wc_feed(e, slab[s], fill[s]); // (after an error: keep draining so that the reader ends)
+        if (rc == WC_OK) rc = wc_feed(e, at[s], fill[s]); // (after an error: keep draining so that the reader ends)
         {
             std::lock_guard<std::mutex> lk(mu);
             consumed++;
@@ -99,6 +129,7 @@ static int stream_file(wc_engine *e, FILE *f) {
     }
     reader.join();
     for (int i = 0; i < kSlabs; i++) wc_host_free(slab[i]);
+    if (rc == WC_OK && io_error) rc = WC_ERR_INVALID;
     return rc;
 }
 
@@ -134,25 +165,25 @@ struct ShardJob {
     std::string err;
 };
 
-// Feeds bytes [lo, hi) of the input to engine `e` (from memory, or from the file through two pinned slabs).
-static int feed_range(wc_engine *e, int fd, const std::vector<char> *mem, uint64_t lo, uint64_t hi) {
+// Feeds bytes [lo, hi) of the input to engine `e` (from memory, or from the file through a pinned slab).
+static int feed_range(wc_engine *e, int fd, bool direct, const std::vector<char> *mem, uint64_t lo, uint64_t hi) {
     if (mem) return hi > lo ? wc_feed(e, mem->data() + lo, hi - lo) : WC_OK;
     constexpr size_t kSlab = (size_t)64 << 20;
     char *slab = nullptr;
     if (wc_host_alloc((void **)&slab, kSlab) != WC_OK) return WC_ERR_NOMEM;
     int rc = WC_OK;
     for (uint64_t pos = lo; pos < hi && rc == WC_OK;) {
-        const size_t want = (size_t)((hi - pos) < kSlab ? (hi - pos) : kSlab);
-        const ssize_t k = pread(fd, slab, want, (off_t)pos);
+        char *at = nullptr;
+        const ssize_t k = read_at(fd, direct, slab, kSlab, pos, (size_t)((hi - pos) < kSlab ? (hi - pos) : kSlab), &at);
         if (k <= 0) { rc = WC_ERR_INVALID; break; }
-        rc = wc_feed(e, slab, (size_t)k);
+        rc = wc_feed(e, at, (size_t)k);
         pos += (uint64_t)k;
     }
     wc_host_free(slab);
     return rc;
 }
 
-static int run_multi_gpu(const wc_config &base, int n_gpus, int fd, const std::vector<char> *mem, uint64_t size, wc_result **out,
+static int run_multi_gpu(const wc_config &base, int n_gpus, int fd, int bulk_fd, bool direct, const std::vector<char> *mem, uint64_t size, wc_result **out,
                          std::string *err) {
     std::vector<uint64_t> cut(n_gpus + 1, size);
     cut[0] = 0;
@@ -180,7 +211,7 @@ static int run_multi_gpu(const wc_config &base, int n_gpus, int fd, const std::v
         for (int r = 0; r < n_gpus; r++)
             th.emplace_back([&, r] { // one feeder per GPU; a sender pushes its table as soon as its shard is counted
                 ShardJob &j = job[r];
-                j.rc = feed_range(j.e, fd, mem, cut[r], cut[r + 1]);
+                j.rc = feed_range(j.e, bulk_fd, direct, mem, cut[r], cut[r + 1]);
                 if (j.rc == WC_OK && r != 0) j.rc = wc_peer_push(j.e, nullptr);
                 if (j.rc == WC_OK) j.rc = wc_sync(j.e);
                 if (j.rc != WC_OK) j.err = wc_last_error(j.e);
@@ -200,7 +231,7 @@ static int run_multi_gpu(const wc_config &base, int n_gpus, int fd, const std::v
 
 int main(int argc, char **argv) {
     const char *path = "test.txt";
-    bool echo = true, json = false;
+    bool echo = true, json = false, direct_io = false;
     int n_gpus = 1;
     wc_config cfg;
     wc_config_default(&cfg);
@@ -208,6 +239,7 @@ int main(int argc, char **argv) {
         const char *a = argv[i];
         if (!strcmp(a, "--no-echo")) echo = false;
         else if (!strcmp(a, "--json")) json = true;
+        else if (!strcmp(a, "--direct-io")) direct_io = true;
         else if (!strcmp(a, "--strict-ref")) cfg.flags |= WC_FLAG_STRICT_REF;
         else if (!strcmp(a, "--map=lower")) cfg.mapper = WC_MAP_LOWER_ASCII;
         else if (!strcmp(a, "--map=identity")) cfg.mapper = WC_MAP_IDENTITY;
@@ -235,6 +267,21 @@ int main(int argc, char **argv) {
         echo_input(data, (cfg.flags & WC_FLAG_STRICT_REF) ? 99 : 0);
     }
 
+    // bulk reads of a file that is not echoed: its own descriptor, O_DIRECT when asked for and available
+    // (tmpfs and some overlay file systems refuse it: buffered reads then, said once on stderr)
+    int bulk_fd = f ? fileno(f) : -1;
+    bool direct = false;
+    if (f && direct_io) {
+        int dfd = open(path, O_RDONLY | O_DIRECT);
+        if (dfd >= 0) { // some file systems accept the flag and refuse the read: try one block
+            void *blk = nullptr;
+            if (posix_memalign(&blk, kIoAlign, kIoAlign) != 0 || pread(dfd, blk, kIoAlign, 0) < 0) { close(dfd); dfd = -1; }
+            free(blk);
+        }
+        if (dfd >= 0) { bulk_fd = dfd; direct = true; }
+        else fprintf(stderr, "wordcount: --direct-io: O_DIRECT refused for %s (%s), reading through the page cache\n", path, strerror(errno));
+    }
+
     wc_engine *e = nullptr;
     wc_result *r = nullptr;
     int rc;
@@ -249,14 +296,14 @@ int main(int argc, char **argv) {
             if (fstat(fd, &st) != 0) { fprintf(stderr, "wordcount: cannot stat %s\n", path); return 1; }
             size = (uint64_t)st.st_size;
         }
-        rc = run_multi_gpu(cfg, n_gpus, fd, present ? &data : nullptr, size, &r, &err);
+        rc = run_multi_gpu(cfg, n_gpus, fd, bulk_fd, direct, present ? &data : nullptr, size, &r, &err);
         if (f) fclose(f);
         if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), err.c_str()); return 1; }
     } else {
         rc = wc_create(&e, &cfg);
         if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(nullptr)); return 1; }
         if (present) rc = wc_feed(e, data.data(), data.size());
-        else if (f) { rc = stream_file(e, f); fclose(f); }
+        else if (f) { rc = stream_file(e, bulk_fd, direct); fclose(f); }
         if (rc == WC_OK) rc = wc_finish(e, &r);
         if (rc != WC_OK) { fprintf(stderr, "wordcount: %s: %s\n", wc_strerror(rc), wc_last_error(e)); wc_destroy(e); return 1; }
     }
@@ -276,5 +323,6 @@ int main(int argc, char **argv) {
     }
     wc_result_free(r);
     if (e) wc_destroy(e);
+    if (direct) close(bulk_fd);
     return 0; // main.cu:221
 }

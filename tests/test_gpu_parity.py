@@ -147,6 +147,31 @@ def test_cli_gpus_flag(pkg, golden):
                 assert one.stdout == exp.stdout, name
 
 
+def test_cli_direct_io(pkg):
+    """wordcount --no-echo --direct-io: the reader thread fills the pinned slabs with O_DIRECT reads (no page
+    cache copy; buffered where the file system refuses it).  Same stdout as the buffered run and the oracle's
+    rows, on one GPU and -- shards starting at unaligned line starts -- on several."""
+    import torch
+    from tools.corpus import Corpus
+    exe = os.path.join(ROOT, "cuda-mapreduce_b200", "wordcount")
+    data = Corpus(2, total_bytes=(96 << 20) + 12345).bytes().tobytes()
+    data = data[:data.rindex(b"\n") + 1]
+    with tempfile.TemporaryDirectory(dir=ROOT) as td:  # (the repository's file system, not a tmpfs)
+        p = os.path.join(td, "corpus.txt")
+        with open(p, "wb") as f:
+            f.write(data)
+        plain = subprocess.run([exe, p, "--no-echo"], cwd=td, capture_output=True, timeout=300)
+        direct = subprocess.run([exe, p, "--no-echo", "--direct-io"], cwd=td, capture_output=True, timeout=300)
+        assert plain.returncode == 0 and direct.returncode == 0, (plain.stderr, direct.stderr)
+        assert direct.stdout == plain.stdout
+        exp = O.fast(data, render=True)
+        assert plain.stdout == b"Input Data:\n" + exp.stdout[exp.stdout.index(b"-----"):]
+        if torch.cuda.device_count() >= 2:
+            many = subprocess.run([exe, p, "--no-echo", "--direct-io", "--gpus=2"], cwd=td, capture_output=True, timeout=300)
+            assert many.returncode == 0, many.stderr
+            assert many.stdout == plain.stdout
+
+
 REF_LINKED = os.path.join(ROOT, "oracle", "_ref", "main_linked")
 
 
