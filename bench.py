@@ -403,7 +403,8 @@ def run_workload(cx, workload, steps, warmup, primary):
     if rank == 0:
         full = eng.finish(keep_rows=want_rows)
         result_check = {"rows": full.n_rows, "total": full.total, "n_flush": full.stats["n_flush"], "stop": full.stats["stop"],
-                        "path_used": full.stats.get("path_used"), "checksum": full.checksum,
+                        "path_used": full.stats.get("path_used"), "tokenizing_warps": full.stats.get("tokenizing_warps"),
+                        "checksum": full.checksum,
                         "rows_sha256": rows_digest(full.rows) if want_rows else None}
         del full
     cx.barrier()

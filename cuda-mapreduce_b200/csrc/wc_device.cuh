@@ -45,6 +45,10 @@ constexpr int kTile = 1024;                // bytes per warp-tile: two sub-tiles
 constexpr int kWarps = WC_WARPS;           // warps per CTA
 constexpr int kConsumers = WC_CONSUMERS;   // of which only insert deferred words into the global tables
 constexpr int kProducers = kWarps - kConsumers; // the others tokenize and count; the text is split over these
+// The split is a launch parameter (Launch::producers, Launch::smem_entries): kProducers / kConsumers are the
+// default one (config 2: 17 % of the words go to the consumers), kProducersHeavy the one for text that sends
+// more of its words to the global tables (config 3: 18 + 10 warps runs 13 % faster there, 5 % slower on config 2).
+constexpr int kProducersHeavy = kProducers - 2;
 constexpr int kThreads = kWarps * 32;
 constexpr int kBufBytes = 1072;            // one tile buffer: 16 B tail of the previous tile + tile + slack
 constexpr int kRingBytes = 2 * kBufBytes;  // per producer warp: two buffers, the next tile lands by cp.async
@@ -63,12 +67,18 @@ constexpr u32 kStageCap = WC_STAGE;              // per producer warp: deferred 
 constexpr int kStageBytes = kStageCap * 16;
 constexpr size_t kWarpSmemBytes = kRingBytes + kDlBytes + kStageBytes;
 constexpr size_t kDefRingBytes = (size_t)kDefRing * 16;
-constexpr u32 kSmemEntries = (u32)((232448 - 256 - kDefRingBytes - kProducers * kWarpSmemBytes) / 16) & ~31u;
-constexpr size_t kSmemTableBytes = (size_t)kSmemEntries * 16; // the per-CTA table gets what is left
-constexpr size_t kSmemTotal = kSmemTableBytes + kDefRingBytes + (size_t)kProducers * kWarpSmemBytes;
+constexpr u32 smem_entries_for(int producers) { // the per-CTA table gets what the producers' areas leave
+    return (u32)((232448 - 256 - kDefRingBytes - (size_t)producers * kWarpSmemBytes) / 16) & ~31u;
+}
+constexpr u32 kSmemEntries = smem_entries_for(kProducers);
+constexpr size_t smem_total_for(int producers) {
+    return (size_t)smem_entries_for(producers) * 16 + kDefRingBytes + (size_t)producers * kWarpSmemBytes;
+}
+constexpr size_t kSmemTotal = smem_total_for(kProducers) > smem_total_for(kProducersHeavy) ? smem_total_for(kProducers)
+                                                                                           : smem_total_for(kProducersHeavy); // one size for both splits
 static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
 static_assert(kSmemTotal <= 232448 - 64, "more shared memory than an sm_100 CTA can have");
-static_assert(kConsumers >= 1 && kProducers >= 1 && kDrainBatch % 32 == 0 && kDrainBatch <= 128, "bad build knobs");
+static_assert(kConsumers >= 1 && kProducersHeavy >= 1 && kDrainBatch % 32 == 0 && kDrainBatch <= 128, "bad build knobs");
 static_assert((kDefRing & (kDefRing - 1)) == 0 && kDefRing >= 4 * kDrainBatch, "ring size");
 
 enum : u32 { kErrWordFull = 1u, kErrLongFull = 2u, kErrArenaFull = 4u, kErrWordTooLong = 8u, kErrRingTimeout = 16u,
@@ -92,6 +102,7 @@ struct Status {
     u32 err;
     u64 job_bytes;    // wc_peer_pull_device: the counters above describe the whole job (job_set), of this many bytes
     u64 job_set;
+    u64 own_words;    // with job_set: the non-empty words this engine counted itself (note_consumer_load wants its own shard's)
     u64 dbg[8];       // WC_PROFILE builds: consumer cycles (wait, claim, global), batches; producer ring-full cycles, total
 };
 
@@ -138,6 +149,8 @@ struct Launch {
     u64 n;
     u64 base;           // offset of buf[0] in the whole input
     u32 tiles_per_warp;
+    u32 producers;      // count_kernel: tokenizing warps per CTA (kProducers or kProducersHeavy); the rest are consumers
+    u32 smem_entries;   // count_kernel: entries of the CTA's shared-memory table = smem_entries_for(producers)
     int last_piece;     // the input ends with this piece
     int negate;         // roll-back launch: subtract everything at or after Status::stop
     int strict;         // read lines in pieces of kLineCap bytes like the reference's fgets does (main.cu:175,179)
@@ -784,6 +797,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
     const u32 lane = lane_id();
     const Tables &T = *Tp;
     const u64 delta = Lp->negate ? ~0ull : 1ull;
+    const u32 n_producers = Lp->producers, n_entries = Lp->smem_entries;
     constexpr int R = kDrainBatch / 32;
     u32 n_wnew = 0, n_xnew = 0, n_spill = 0, n_long = 0;
 #ifdef WC_PROFILE
@@ -803,14 +817,14 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
         __syncwarp();
         for (const u32 last = b + kDrainBatch - 1;;) {
             if ((lds_volatile_u32(&ring[last & (kDefRing - 1)].w) >> 16) == (0x8000u | ring_lap(last))) break;
-            if (lds_volatile_u32(&ctl->done) == (u32)kProducers || ++spins > (1u << 23)) break;
+            if (lds_volatile_u32(&ctl->done) == n_producers || ++spins > (1u << 23)) break;
             __nanosleep(spins < 2 ? WC_SLEEP0 : WC_SLEEP1); // a batch takes a few microseconds to fill: do not burn issue slots polling
         }
 #endif
         u32 polls = spins > (1u << 23) ? spins : 0; // (counted per pass of this loop, which the vote below keeps in step)
         polls = __shfl_sync(0xFFFFFFFFu, polls, 0);
         for (;;) { // take the batch
-            const bool all_done = lds_volatile_u32(&ctl->done) == (u32)kProducers; // read before tail: tail is final once this holds
+            const bool all_done = lds_volatile_u32(&ctl->done) == n_producers; // read before tail: tail is final once this holds
             const u32 tail = lds_volatile_u32(&ctl->tail);
             bool ok = true;
 #pragma unroll
@@ -866,7 +880,7 @@ void consume_deferred(uint4 *ring, DefCtl *ctl, const Launch *Lp, const Tables *
             if (len == 0 || len > 8) continue;
             if (todo & (1u << j)) { n_spill++; continue; }
             const u64 k0 = (u64)rec[j].x | ((u64)rec[j].y << 32);
-            const u32 sidx = __umulhi(hash32_of_cta(rec[j].x, rec[j].y), kSmemEntries);
+            const u32 sidx = __umulhi(hash32_of_cta(rec[j].x, rec[j].y), n_entries);
             const u64 old = atoms_cas_u64(&tab[sidx], 0ull, k0);
             if (old == 0 || old == k0) {
                 u32 *cell = reinterpret_cast<u32 *>(&tab[sidx]);
@@ -954,8 +968,9 @@ template <class Map>
 __global__ void __launch_bounds__(kThreads, 1)
 count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T) {
     uint4 *tab = reinterpret_cast<uint4 *>(wc_smem);
-    uint4 *def_ring = reinterpret_cast<uint4 *>(wc_smem + kSmemTableBytes);
-    unsigned char *warp_all = wc_smem + kSmemTableBytes + kDefRingBytes;
+    const u32 n_producers = L.producers, n_entries = L.smem_entries;
+    uint4 *def_ring = reinterpret_cast<uint4 *>(wc_smem + (size_t)n_entries * 16);
+    unsigned char *warp_all = wc_smem + (size_t)n_entries * 16 + kDefRingBytes;
     __shared__ u32 s_first_ws;
     __shared__ u64 s_stop;
     __shared__ DefCtl s_ctl;
@@ -1002,13 +1017,13 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     }
     const u32 delta32 = L.negate ? 0xFFFFFFFFu : 1u;
 
-    for (u32 i = tid; i < kSmemEntries; i += kThreads) tab[i] = make_uint4(0, 0, 0, 0xFFFFFFFFu);
+    for (u32 i = tid; i < n_entries; i += kThreads) tab[i] = make_uint4(0, 0, 0, 0xFFFFFFFFu);
     for (u32 i = tid; i < kDefRing; i += kThreads) def_ring[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) { s_ctl.tail = 0; s_ctl.head = 0; s_ctl.done = 0; s_ctl.abort_flag = 0; }
     __syncthreads();
 
-    const u64 cta_base = (u64)blockIdx.x * kProducers * L.tiles_per_warp * kTile; // buffer-relative
-    if (warp >= (u32)kProducers) { // ---- consumer warps: everything that needs global memory
+    const u64 cta_base = (u64)blockIdx.x * n_producers * L.tiles_per_warp * kTile; // buffer-relative
+    if (warp >= n_producers) { // ---- consumer warps: everything that needs global memory
         consume_deferred<Map>(def_ring, &s_ctl, &L, &T, cta_base, tab);
     } else { // ---- producer warps: tokenize and count
 
@@ -1019,7 +1034,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     u32 n_staged = 0; // warp-uniform
 
     const u32 tiles_total = (u32)((L.n + kTile - 1) / kTile);
-    const u32 gwarp = blockIdx.x * kProducers + warp;
+    const u32 gwarp = blockIdx.x * n_producers + warp;
     u32 t0 = gwarp * L.tiles_per_warp < tiles_total ? gwarp * L.tiles_per_warp : tiles_total;
     const u32 t1 = t0 + L.tiles_per_warp < tiles_total ? t0 + L.tiles_per_warp : tiles_total;
     if (range_lo > 0 && t0 < t1) { // roll-back: start at the tile that holds range_lo
@@ -1282,7 +1297,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
                     }
 
                     // single-probe shared-memory table
-                    const u32 slot = __umulhi(hash32_of_cta(klo, khi), kSmemEntries);
+                    const u32 slot = __umulhi(hash32_of_cta(klo, khi), n_entries);
                     const uint4 ent = tab[slot];
                     const bool hit = word && len <= 8 && ent.x == klo && ent.y == khi;
                     const u32 rel = relT + (u32)e;
@@ -1343,7 +1358,7 @@ count_kernel(const __grid_constant__ Launch L, const __grid_constant__ Tables T)
     // ---- flush the CTA's table into the global one
     __syncthreads();
     u32 n_wnew = 0;
-    for (u32 i = tid; i < kSmemEntries; i += kThreads) {
+    for (u32 i = tid; i < n_entries; i += kThreads) {
         const uint4 ent = tab[i];
         if ((ent.x | ent.y) != 0 && ent.z != 0) {
             const u64 key = (u64)ent.x | ((u64)ent.y << 32);

@@ -56,6 +56,9 @@ struct wc_engine {
     wc::WarpSummary *d_ws = nullptr;
     u32 n_ws = 0;
     wc::Status *h_status = nullptr; // pinned
+    wc::Status *h_prev = nullptr;   // pinned: the counters of a job that ended in wc_reset (poll_job_snapshot)
+    cudaEvent_t ev_prev = nullptr;
+    bool prev_pending = false;
 
     // streaming (allocated on first wc_feed)
     size_t chunk_cap = 0;
@@ -71,6 +74,8 @@ struct wc_engine {
     // engine's first job, then of every finished job (the next job of the same engine follows it)
     bool auto_path = false, auto_decided = false;
     double auto_ratio = -1.0;   // distinct words / words last seen (probe or finished job); < 0: none yet
+    u32 producers = wc::kProducers; // count_kernel's warp split for the next launch (note_consumer_load)
+    u32 last_tokenizing_warps = 0;  // what the job's last forward launch ran with (wc_stats.tokenizing_warps)
     wc::EmitBuf em{};           // device buffers; em.cursor is always allocated in sort mode
     u64 em_bound = 0;           // upper bound of records written so far (pieces launched)
     ulonglong2 *so_key = nullptr; u64 *so_count = nullptr, *so_first = nullptr; // wc_aggregate()'s output
@@ -176,6 +181,8 @@ static int reset_device_state(wc_engine *e) {
     return WC_OK;
 }
 
+static void poll_job_snapshot(wc_engine *e);
+
 // ----------------------------------------------------------------- C ABI
 
 extern "C" {
@@ -235,6 +242,8 @@ void wc_destroy(wc_engine *e) {
     if (e->em.end) cudaFree(e->em.end);
     if (e->d_ovf) cudaFree(e->d_ovf);
     if (e->h_status) cudaFreeHost(e->h_status);
+    if (e->h_prev) cudaFreeHost(e->h_prev);
+    if (e->ev_prev) cudaEventDestroy(e->ev_prev);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     delete e;
@@ -272,6 +281,8 @@ static int create_impl(wc_engine *e, const wc_config *cfg) {
     CK(cudaFuncSetAttribute(wc::count_kernel2<wc::MapLowerAscii>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wc::k2SmemTotal));
     CK(cudaMalloc((void **)&e->d_status, sizeof(wc::Status)));
     CK(cudaMallocHost((void **)&e->h_status, sizeof(wc::Status)));
+    CK(cudaMallocHost((void **)&e->h_prev, sizeof(wc::Status)));
+    CK(cudaEventCreateWithFlags(&e->ev_prev, cudaEventDisableTiming));
     e->T.st = e->d_status;
     e->n_ws = (u32)e->grid * kMaxTokenWarps;
     CK(cudaMalloc((void **)&e->d_ws, sizeof(wc::WarpSummary) * e->n_ws));
@@ -317,6 +328,12 @@ int wc_reset(wc_engine *e) {
     if (!e) return WC_ERR_INVALID;
     CK(cudaSetDevice(e->device));
     CK(cudaStreamSynchronize(e->copy_stream));
+    poll_job_snapshot(e);
+    if (e->consumed > 0 && !e->prev_pending && !e->sort_mode && e->cfg.job == WC_JOB_WORDCOUNT) {
+        CK(cudaMemcpyAsync(e->h_prev, e->d_status, sizeof(wc::Status), cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaEventRecord(e->ev_prev, e->stream));
+        e->prev_pending = true;
+    }
     int rc = reset_device_state(e);
     if (rc != WC_OK) return rc;
     e->carry.clear();
@@ -353,6 +370,31 @@ static int grow_word_table(wc_engine *e, u32 new_log2) {
     return WC_OK;
 }
 
+// count_kernel's warp split follows the text: the share of words that the tokenizing warps hand to the consumer
+// warps (misses of the CTA's table and words of 9+ bytes) is read from the counters whenever the host looks at
+// them anyway -- after the first pieces of a fed job, and at wc_finish for the job after it.  Measured on one
+// B200 (profiles/r2_kernel_experiments.txt, F): at 0.17 (config 2) 20 + 8 warps is the fastest split, 18 + 10
+// costs 5 %; at 0.27 (config 3) 18 + 10 is 13 % faster; at 0.78 (config 5: almost every word is a new table
+// entry, the consumers wait for DRAM whatever their number) more consumers do not help.
+constexpr u64 kLoadMinWords = 100000;
+static void note_consumer_load(wc_engine *e, const wc::Status &st) {
+    static const int forced = [] { const char *v = getenv("WC_PRODUCERS"); return v ? atoi(v) : 0; }();
+    if (forced) { e->producers = forced == wc::kProducersHeavy ? (u32)wc::kProducersHeavy : (u32)wc::kProducers; return; }
+    const u64 words = st.job_set ? st.own_words : st.n_flush - st.n_empty; // (after a peer pull the counters are the job's)
+    if (words < kLoadMinWords) return;
+    const double load = (double)(st.n_spill + st.n_long) / (double)words;
+    e->producers = (load >= 0.22 && load < 0.60) ? (u32)wc::kProducersHeavy : (u32)wc::kProducers;
+}
+
+// A job that ends in wc_reset without a wc_finish (a caller that only wants device-side tables, a benchmark
+// loop) is looked at too, without a host wait: wc_reset queues a copy of the counters in front of the reset,
+// and whoever launches next reads it once the copy has completed.
+static void poll_job_snapshot(wc_engine *e) {
+    if (!e->prev_pending || cudaEventQuery(e->ev_prev) != cudaSuccess) return;
+    e->prev_pending = false;
+    note_consumer_load(e, *e->h_prev);
+}
+
 // After a sync: if words overflowed the table (or it is more than half full), grow it and replay the
 // overflow log.  Leaves e->h_status up to date.  No word is ever dropped: wc_device.cuh logs what the
 // table could not take.
@@ -363,6 +405,7 @@ static int settle_tables(wc_engine *e) {
         CK(cudaStreamSynchronize(e->stream));
         const wc::Status st = *e->h_status;
         const u64 cap = 1ull << e->T.w_log2;
+        note_consumer_load(e, st);
         if ((st.err & wc::kErrWordFull) != 0) return WC_OK; // the log itself overflowed: reported by the caller
         if (st.ovf_count == 0 && st.w_entries * 2 <= cap) return WC_OK;
         u32 want = e->T.w_log2;
@@ -520,7 +563,9 @@ static bool forward_uses_kernel2(uint32_t flags, bool sort_mode, bool strict) {
 // piece is too large for one launch (a CTA's range must fit 32-bit offsets).
 static bool launch_count(cudaStream_t stream, int grid, uint32_t mapper, wc::Launch L, const wc::Tables &T, bool kernel2) {
     const u64 tiles = (L.n + wc::kTile - 1) / wc::kTile;
-    const u64 per_cta = kernel2 ? wc::k2Warps : wc::kProducers;
+    if (L.producers != (u32)wc::kProducersHeavy) L.producers = wc::kProducers;
+    L.smem_entries = L.producers == (u32)wc::kProducersHeavy ? wc::smem_entries_for(wc::kProducersHeavy) : wc::kSmemEntries;
+    const u64 per_cta = kernel2 ? wc::k2Warps : L.producers;
     const u64 warps = (u64)grid * per_cta;
     const u64 tpw = (tiles + warps - 1) / warps;
     if (tpw * per_cta * wc::kTile >= 0xFFFFFFF0ull) return false;
@@ -608,11 +653,14 @@ static int launch_piece(wc_engine *e, const uint8_t *dev, size_t n, int last_pie
     }
     const bool strict = (e->cfg.flags & WC_FLAG_STRICT_REF) != 0;
     const bool k2 = forward_uses_kernel2(e->cfg.flags, e->sort_mode, strict);
+    poll_job_snapshot(e);
     wc::Launch L{};
     L.buf = dev; L.n = n; L.base = e->cfg.base_offset + e->consumed;
     L.last_piece = last_piece; L.negate = 0;
     L.strict = strict;
-    L.ws = e->d_ws; L.n_ws = (u32)e->grid * (k2 ? wc::k2Warps : wc::kProducers); // one summary per tokenizing warp
+    L.producers = (k2 || strict || e->sort_mode) ? (u32)wc::kProducers : e->producers;
+    L.ws = e->d_ws; L.n_ws = (u32)e->grid * (k2 ? wc::k2Warps : L.producers); // one summary per tokenizing warp
+    e->last_tokenizing_warps = k2 ? wc::k2Warps : L.producers;
     if (e->sort_mode) {
         int rc = ensure_emit_capacity(e, n);
         if (rc != WC_OK) return rc;
@@ -859,6 +907,7 @@ static int finish_line_lengths(wc_engine *e, wc_result **out) {
 // The path this job took, and what it says about the next one (WC_PATH_AUTO).
 static void note_job_path(wc_engine *e, wc_stats *s) {
     s->path_used = e->sort_mode ? WC_PATH_SORT : WC_PATH_HASH;
+    s->tokenizing_warps = e->last_tokenizing_warps;
     const u64 words = s->n_flush - s->n_empty;
     if (words >= kAutoProbeMinWords) e->auto_ratio = (double)s->n_distinct / (double)words;
     s->distinct_ratio = words ? (double)s->n_distinct / (double)words : 0.0;
@@ -883,6 +932,7 @@ int wc_finish(wc_engine *e, wc_result **out) {
     const double t_settle = since();
     e->carry.clear();
     const wc::Status st = *e->h_status;
+    note_consumer_load(e, st);
     if (st.job_set) { e->job_stats_set = true; e->job_bytes = st.job_bytes; } // (wc_peer_pull_device set the job's counters on the device)
     if (st.err & wc::kErrPeer) {
         e->err = "peer gather: a sender's push did not arrive, or its tables / landing area overflowed";

@@ -265,6 +265,7 @@ __global__ void peer_wait_reduce_kernel(uint8_t *area0, u64 stride, u32 n_ranks,
         }
         if (s_stop != ~0ull) stop = s_stop;
     }
+    st->own_words = st->n_flush - st->n_empty;
     st->n_flush = n_flush; st->n_empty = n_empty; st->lost_empty = lost; st->p0 = p0; st->stop = stop; st->p0_found = p0_found;
     st->job_bytes = bytes; st->job_set = 1;
     if (s_failed) atomicOr(&st->err, kErrPeer);

@@ -49,6 +49,7 @@ class Stats(C.Structure):
         ("stop", C.c_uint64), ("n_distinct", C.c_uint64), ("n_long_words", C.c_uint64), ("n_spilled", C.c_uint64),
         ("n_slow_tiles", C.c_uint64), ("table_grows", C.c_uint64), ("device_ms", C.c_double),
         ("count_kernel_ms", C.c_double), ("path_used", C.c_uint64), ("distinct_ratio", C.c_double),
+        ("tokenizing_warps", C.c_uint64),
     ]
 
 

@@ -129,6 +129,9 @@ typedef struct wc_stats {
     double count_kernel_ms;  /* of which the tokenizer/count kernel alone */
     uint64_t path_used;      /* WC_PATH_HASH or WC_PATH_SORT: what wc_config.path = WC_PATH_AUTO chose for this job */
     double distinct_ratio;   /* distinct words / non-empty words of this job (what WC_PATH_AUTO goes by) */
+    uint64_t tokenizing_warps; /* of the count kernel's 28 warps per CTA, how many tokenized in this job's last launch (the
+                                * others insert into the device tables): 20, or 18 once the engine has seen text that sends
+                                * 22-60 % of its words there; 28 with WC_FLAG_LANE_SERIAL */
 } wc_stats;
 
 WC_API void wc_config_default(wc_config *cfg);

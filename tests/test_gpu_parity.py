@@ -4,6 +4,7 @@ the splitter's counters.  Run on the B200 box with `pytest -m gpu`."""
 import os
 import random
 import subprocess
+import sys
 import tempfile
 
 import numpy as np
@@ -766,6 +767,60 @@ def test_auto_path_switches_on_distinct_ratio(pkg, monkeypatch):
         e.count_device(dev.data_ptr(), dev.numel(), last_piece=True)  # (device-resident input goes the same way)
         got = e.finish()
         assert got.stats["path_used"] == pkg.PATH_HASH and same(got, exp_adv)  # follows the Zipf job: hash, still exact
+
+
+def test_warp_split_follows_the_text(pkg):
+    """count_kernel's split into tokenizing and inserting warps (Launch::producers) follows the share of words
+    the previous launches handed to the inserting warps: 20 + 8 by default, 18 + 10 after text that sends
+    22-60 % of its words to the device tables -- learned at wc_finish, after the first pieces of a fed job, or
+    (no host wait) from the counters wc_reset copies out.  Whatever the split, the rows are the oracle's."""
+    import torch
+    from tools.corpus import Corpus
+    heavy = Corpus(3, total_bytes=64 << 20).bytes()
+    light = np.frombuffer(b"the quick brown fox jumps over the lazy dog\n" * 400000, dtype=np.uint8).copy()
+    exp_h, exp_l = O.fast_mt(heavy), O.fast_mt(light)
+    dev_h, dev_l = torch.from_numpy(heavy).cuda(), torch.from_numpy(light).cuda()
+
+    def load(r):
+        return (r.stats["n_spilled"] + r.stats["n_long_words"]) / (r.stats["n_flush"] - r.stats["n_empty"])
+
+    with pkg.Engine(short_table_log2=21, long_table_log2=18, path=pkg.PATH_HASH) as e:
+        e.count_device(dev_h.data_ptr(), dev_h.numel())
+        r1 = e.finish()
+        assert r1.stats["tokenizing_warps"] == 20 and r1.pairs() == exp_h.pairs() and r1.total == exp_h.total
+        assert 0.22 <= load(r1) < 0.60, load(r1)       # the sample is what this test needs it to be
+        e.reset()
+        e.count_device(dev_h.data_ptr(), dev_h.numel())
+        r2 = e.finish()                                 # learned from the job before, at its wc_finish
+        assert r2.stats["tokenizing_warps"] == 18 and r2.pairs() == exp_h.pairs() and r2.total == exp_h.total
+        e.reset()
+        e.count_device(dev_l.data_ptr(), dev_l.numel())
+        e.sync()
+        e.reset()                                       # a job dropped without wc_finish: its counters are copied out ...
+        e.sync()
+        e.count_device(dev_l.data_ptr(), dev_l.numel()) # ... and read here
+        r3 = e.finish()
+        assert load(r3) < 0.22, load(r3)
+        assert r3.stats["tokenizing_warps"] == 20 and r3.pairs() == exp_l.pairs() and r3.total == exp_l.total
+    # a fed job switches between its pieces (the counters are read after each of the first four): the first
+    # piece is the text above, so the second one runs with what that one showed
+    twice = np.concatenate([heavy, heavy])
+    exp_t = O.fast_mt(twice)
+    with pkg.Engine(short_table_log2=21, long_table_log2=18, chunk_bytes=heavy.size, path=pkg.PATH_HASH) as e:
+        e.feed(twice)
+        r4 = e.finish()
+        assert r4.stats["tokenizing_warps"] == 18 and r4.pairs() == exp_t.pairs() and r4.total == exp_t.total
+
+
+def test_forced_warp_split_passes_the_parity_cases():
+    """The 18 + 10 split on every input of the small parity tests (WC_PRODUCERS=18 is read once per process,
+    hence the child pytest)."""
+    env = dict(os.environ, WC_PRODUCERS="18")
+    sel = "golden_vectors or fuzz or tile_and_chunk or stop_rules or crlf or ragged or config2_sample or config5_sample or mapper_policy"
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(ROOT, "tests", "test_gpu_parity.py"), "-x", "-q", "-k", sel,
+                        "-p", "no:cacheprovider"], env=env, cwd=ROOT, capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
 
 
 def test_sort_path_matches_oracle(pkg, golden):
