@@ -74,8 +74,16 @@ constexpr u32 kSmemEntries = smem_entries_for(kProducers);
 constexpr size_t smem_total_for(int producers) {
     return (size_t)smem_entries_for(producers) * 16 + kDefRingBytes + (size_t)producers * kWarpSmemBytes;
 }
-constexpr size_t kSmemTotal = smem_total_for(kProducers) > smem_total_for(kProducersHeavy) ? smem_total_for(kProducers)
-                                                                                           : smem_total_for(kProducersHeavy); // one size for both splits
+// Splits a launch may ask for (the engine uses kProducers and kProducersHeavy; WC_PRODUCERS can force any of them
+// for an experiment).  One dynamic shared-memory size serves them all: the table takes what the producers leave.
+constexpr int kMinProducers = kWarps / 2, kMaxProducers = kWarps - 4;
+constexpr size_t smem_total_max() {
+    size_t m = 0;
+    for (int p = kMinProducers; p <= kMaxProducers; p++) m = smem_total_for(p) > m ? smem_total_for(p) : m;
+    return m;
+}
+constexpr size_t kSmemTotal = smem_total_max();
+static_assert(kProducers <= kMaxProducers && kProducersHeavy >= kMinProducers, "the engine's splits must be launchable");
 static_assert(kWarpSmemBytes % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
 static_assert(kSmemTotal <= 232448 - 64, "more shared memory than an sm_100 CTA can have");
 static_assert(kConsumers >= 1 && kProducersHeavy >= 1 && kDrainBatch % 32 == 0 && kDrainBatch <= 128, "bad build knobs");

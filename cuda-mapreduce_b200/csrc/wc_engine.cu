@@ -379,7 +379,7 @@ static int grow_word_table(wc_engine *e, u32 new_log2) {
 constexpr u64 kLoadMinWords = 100000;
 static void note_consumer_load(wc_engine *e, const wc::Status &st) {
     static const int forced = [] { const char *v = getenv("WC_PRODUCERS"); return v ? atoi(v) : 0; }();
-    if (forced) { e->producers = forced == wc::kProducersHeavy ? (u32)wc::kProducersHeavy : (u32)wc::kProducers; return; }
+    if (forced) { e->producers = (u32)forced; return; } // (launch_count falls back to the default split if it is out of range)
     const u64 words = st.job_set ? st.own_words : st.n_flush - st.n_empty; // (after a peer pull the counters are the job's)
     if (words < kLoadMinWords) return;
     const double load = (double)(st.n_spill + st.n_long) / (double)words;
@@ -563,8 +563,8 @@ static bool forward_uses_kernel2(uint32_t flags, bool sort_mode, bool strict) {
 // piece is too large for one launch (a CTA's range must fit 32-bit offsets).
 static bool launch_count(cudaStream_t stream, int grid, uint32_t mapper, wc::Launch L, const wc::Tables &T, bool kernel2) {
     const u64 tiles = (L.n + wc::kTile - 1) / wc::kTile;
-    if (L.producers != (u32)wc::kProducersHeavy) L.producers = wc::kProducers;
-    L.smem_entries = L.producers == (u32)wc::kProducersHeavy ? wc::smem_entries_for(wc::kProducersHeavy) : wc::kSmemEntries;
+    if (L.producers < (u32)wc::kMinProducers || L.producers > (u32)wc::kMaxProducers) L.producers = wc::kProducers;
+    L.smem_entries = wc::smem_entries_for((int)L.producers);
     const u64 per_cta = kernel2 ? wc::k2Warps : L.producers;
     const u64 warps = (u64)grid * per_cta;
     const u64 tpw = (tiles + warps - 1) / warps;
