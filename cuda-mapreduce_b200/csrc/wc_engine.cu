@@ -390,7 +390,10 @@ static void note_consumer_load(wc_engine *e, const wc::Status &st) {
 // loop) is looked at too, without a host wait: wc_reset queues a copy of the counters in front of the reset,
 // and whoever launches next reads it once the copy has completed.
 static void poll_job_snapshot(wc_engine *e) {
-    if (!e->prev_pending || cudaEventQuery(e->ev_prev) != cudaSuccess) return;
+    if (!e->prev_pending) return;
+    const cudaError_t q = cudaEventQuery(e->ev_prev);
+    if (q == cudaErrorNotReady) { (void)cudaGetLastError(); return; } // (not an error: keep it out of the next CK(cudaGetLastError()))
+    if (q != cudaSuccess) return;                                     // (a real failure surfaces at the caller's next checked call)
     e->prev_pending = false;
     note_consumer_load(e, *e->h_prev);
 }
