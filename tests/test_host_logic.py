@@ -100,6 +100,30 @@ def test_host_reduce_matches_oracle_fuzz():
         assert got.pairs() == ref.pairs() and got.total == ref.total, data
 
 
+def test_host_reduce_large_input_uses_all_threads():
+    """Above 2^18 distinct words the host reduce (the sort path's wc_finish) runs its passes on all cores --
+    bucketed sorts, per-thread histograms -- and must still give the oracle's rows: 400 k distinct words of
+    1..24 bytes over a three-letter alphabet (prefix chains at every length, heads equal on 16 bytes)."""
+    rng = np.random.default_rng(11)
+    n_words = 900_000
+    lens = rng.integers(1, 25, size=n_words)
+    lens[rng.random(n_words) < 0.3] = 12               # enough equal-length words for plenty of repeats
+    total = int(lens.sum()) + n_words
+    buf = np.empty(total, dtype=np.uint8)
+    ends = np.cumsum(lens + 1) - 1                      # where each word's delimiter sits
+    buf[:] = rng.integers(97, 100, size=total, dtype=np.uint8)
+    buf[ends] = 32
+    buf[ends[7::8]] = 10                                # a line feed every eighth word: no blank line, no STOP
+    buf[ends[-1]] = 10
+    data = buf.tobytes()
+    ref = O.fast_mt(data)
+    ex = O.fast(data, O.MODE_EXACT)
+    assert len(ex.rows) > (1 << 18) and ref.n_rows < len(ex.rows)   # large enough, and the prefix rule bites
+    got = finalize_via_product(data)
+    assert got.total == ref.total
+    assert got.pairs() == ref.pairs()
+
+
 def test_render_matches_reference_tail(golden):
     """wc_result_render reproduces main.cu:210-218 byte for byte (golden stdout minus the echo)."""
     for name, data, expect in golden:
